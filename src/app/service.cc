@@ -1,0 +1,283 @@
+#include "app/service.h"
+
+#include <arpa/inet.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <ctime>
+
+#ifndef HOLA_VERSION
+#define HOLA_VERSION "0.0.1-SNAPSHOT"
+#endif
+
+namespace hola {
+
+std::string usage_text() {
+    return "usage: hola [-Dkey=value ...] [options]\n"
+           "\n"
+           "JVM-style definitions (same meaning as for the Java service):\n"
+           "  -Dconf=FILE                 properties file holding the `hello` greeting pattern (hot-reloaded, 5 s)\n"
+           "  -Dhello=PATTERN             greeting pattern; beats the environment and the file\n"
+           "  -Dswarm.http.port=N         listen port (default 8080)\n"
+           "  -Dswarm.bind.address=ADDR   listen address (default 0.0.0.0)\n"
+           "  -Dhystrix.command.default.KEY=V, -Dhystrix.threadpool.default.KEY=V   breaker settings\n"
+           "\n"
+           "Options:\n"
+           "  --conf FILE                 same as -Dconf=FILE\n"
+           "  --port N, --bind ADDR       same as the swarm.* definitions (port 0: pick a free one)\n"
+           "  --threads N                 event-loop threads (default: one per available CPU)\n"
+           "  --cpus LIST                 pin thread i to the i-th CPU of LIST (e.g. 0,1,2,3 or 0-3)\n"
+           "  --accept-mode MODE          reuseport (default; one listener per thread) | rr (one acceptor, round-robin)\n"
+           "  --aloha-url URL             downstream base URL (default http://aloha:8080/)\n"
+           "  --resolve NAME=IPV4         answer lookups of NAME with IPV4 instead of asking the system resolver\n"
+           "  --zipkin-url URL            overrides env ZIPKIN_SERVER_URL; unset/empty disables tracing\n"
+           "  --zipkin-flush-ms N         span reporter period (default 1000)\n"
+           "  --hystrix-config FILE       properties file with hystrix.* keys (default: the reference's config.properties values)\n"
+           "  --deltaspike-properties FILE  extra config source at ordinal 100 (META-INF/apache-deltaspike.properties)\n"
+           "  --webjars-dir DIR           directory served under /webjars/ (Swagger-UI assets)\n"
+           "  --idle-timeout MS           close keep-alive connections idle for MS (default: never)\n"
+           "  --max-header-bytes N        request head limit (default 65536)\n"
+           "  --log-config-reads          print the conf path on every config-file read, as the reference does\n"
+           "  --verbose                   log downstream calls and request failures to stderr\n"
+           "  --quiet                     no start-up/shutdown log lines\n"
+           "  --version, --help\n";
+}
+
+namespace {
+
+bool parse_cpu_list(const std::string& s, std::vector<int>* out) {
+    size_t i = 0;
+    while (i < s.size()) {
+        size_t comma = s.find(',', i);
+        if (comma == std::string::npos) comma = s.size();
+        const std::string part = s.substr(i, comma - i);
+        i = comma + 1;
+        if (part.empty()) continue;
+        const size_t dash = part.find('-');
+        char* end = nullptr;
+        if (dash == std::string::npos) {
+            const long v = std::strtol(part.c_str(), &end, 10);
+            if (*end != '\0' || v < 0) return false;
+            out->push_back(static_cast<int>(v));
+        } else {
+            const std::string lo = part.substr(0, dash), hi = part.substr(dash + 1);
+            const long a = std::strtol(lo.c_str(), &end, 10);
+            if (lo.empty() || *end != '\0' || a < 0) return false;
+            const long b = std::strtol(hi.c_str(), &end, 10);
+            if (hi.empty() || *end != '\0' || b < a) return false;
+            for (long v = a; v <= b; ++v) out->push_back(static_cast<int>(v));
+        }
+    }
+    return !out->empty();
+}
+
+bool parse_uint(const std::string& s, long max, long* out) {
+    if (s.empty() || s.size() > 10) return false;
+    long v = 0;
+    for (char c : s) {
+        if (c < '0' || c > '9') return false;
+        v = v * 10 + (c - '0');
+    }
+    if (v > max) return false;
+    *out = v;
+    return true;
+}
+
+}  // namespace
+
+ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceConfig* cfg, std::string* message) {
+    std::string hystrix_config;
+    auto fail = [&](const std::string& m) {
+        *message = "hola: " + m + "\n";
+        return ParseOutcome::kExitUsage;
+    };
+    auto set_prop = [&](const std::string& k, const std::string& v) { cfg->system_properties.emplace_back(k, v); };
+    for (size_t i = 0; i < args.size(); ++i) {
+        const std::string& a = args[i];
+        auto value = [&](std::string* out) {
+            if (i + 1 >= args.size()) return false;
+            *out = args[++i];
+            return true;
+        };
+        std::string v;
+        long n = 0;
+        if (a.size() > 2 && a[0] == '-' && a[1] == 'D') {
+            const size_t eq = a.find('=');
+            if (eq == std::string::npos) {
+                set_prop(a.substr(2), "");
+            } else {
+                set_prop(a.substr(2, eq - 2), a.substr(eq + 1));
+            }
+        } else if (a == "--conf") {
+            if (!value(&v)) return fail("--conf needs a value");
+            set_prop("conf", v);
+        } else if (a == "--port") {
+            if (!value(&v)) return fail("--port needs a value");
+            set_prop("swarm.http.port", v);
+        } else if (a == "--bind") {
+            if (!value(&v)) return fail("--bind needs a value");
+            set_prop("swarm.bind.address", v);
+        } else if (a == "--threads") {
+            if (!value(&v) || !parse_uint(v, 4096, &n)) return fail("--threads needs a number");
+            cfg->server.threads = static_cast<int>(n);
+        } else if (a == "--cpus") {
+            if (!value(&v) || !parse_cpu_list(v, &cfg->server.cpu_affinity)) return fail("bad --cpus list");
+        } else if (a == "--accept-mode") {
+            if (!value(&v) || (v != "reuseport" && v != "rr")) return fail("--accept-mode is reuseport or rr");
+            cfg->server.reuse_port = v == "reuseport";
+        } else if (a == "--aloha-url") {
+            std::string host, path;
+            uint16_t port = 80;
+            if (!value(&v) || !parse_http_url(v, &host, &port, &path)) return fail("--aloha-url must look like http://host:port/");
+            cfg->app.aloha_host = host;
+            cfg->app.aloha_port = port;
+            cfg->app.aloha_path = path + "/api/aloha-chaining";
+        } else if (a == "--resolve") {
+            if (!value(&v)) return fail("--resolve needs NAME=IPV4");
+            const size_t eq = v.find('=');
+            in_addr addr;
+            if (eq == std::string::npos || eq == 0 || inet_pton(AF_INET, v.substr(eq + 1).c_str(), &addr) != 1)
+                return fail("--resolve needs NAME=IPV4");
+            cfg->static_hosts.emplace_back(v.substr(0, eq), v.substr(eq + 1));
+        } else if (a == "--zipkin-url") {
+            if (!value(&v)) return fail("--zipkin-url needs a value");
+            cfg->zipkin_url = v;
+            cfg->zipkin_url_given = true;
+        } else if (a == "--zipkin-flush-ms") {
+            if (!value(&v) || !parse_uint(v, 3600000, &n) || n == 0) return fail("--zipkin-flush-ms needs a positive number");
+            cfg->zipkin_flush_ms = static_cast<int>(n);
+        } else if (a == "--hystrix-config") {
+            if (!value(&hystrix_config)) return fail("--hystrix-config needs a value");
+        } else if (a == "--deltaspike-properties") {
+            if (!value(&cfg->deltaspike_properties)) return fail("--deltaspike-properties needs a value");
+        } else if (a == "--webjars-dir") {
+            if (!value(&v)) return fail("--webjars-dir needs a value");
+            while (v.size() > 1 && v.back() == '/') v.pop_back();
+            cfg->app.webjars_dir = v;
+        } else if (a == "--idle-timeout") {
+            if (!value(&v) || !parse_uint(v, 86400000, &n)) return fail("--idle-timeout needs milliseconds");
+            cfg->server.idle_timeout_ms = static_cast<int>(n);
+        } else if (a == "--max-header-bytes") {
+            if (!value(&v) || !parse_uint(v, 1 << 30, &n) || n < 256) return fail("--max-header-bytes needs a number >= 256");
+            cfg->server.max_header_bytes = static_cast<size_t>(n);
+        } else if (a == "--log-config-reads") {
+            cfg->log_config_reads = true;
+        } else if (a == "--verbose") {
+            cfg->app.verbose = true;
+        } else if (a == "--quiet") {
+            cfg->quiet = true;
+        } else if (a == "--version") {
+            *message = std::string("hola ") + HOLA_VERSION + "\n";
+            return ParseOutcome::kExitOk;
+        } else if (a == "--help" || a == "-h") {
+            *message = usage_text();
+            return ParseOutcome::kExitOk;
+        } else {
+            *message = "hola: unknown argument: " + a + "\n" + usage_text();
+            return ParseOutcome::kExitUsage;
+        }
+    }
+
+    // Listener settings from the swarm.* definitions (later definitions win, as on the JVM).
+    for (const auto& kv : cfg->system_properties) {
+        long n = 0;
+        if (kv.first == "swarm.http.port") {
+            if (!parse_uint(kv.second, 65535, &n)) return fail("bad port: " + kv.second);
+            cfg->server.port = static_cast<uint16_t>(n);
+        } else if (kv.first == "swarm.bind.address") {
+            cfg->server.bind_address = kv.second;
+        }
+    }
+
+    // Breaker settings: the reference's config.properties values, then an optional file, then
+    // -D definitions (Archaius gives system properties the last word).
+    if (!hystrix_config.empty()) {
+        Properties props;
+        std::string err;
+        if (!props.load_file(hystrix_config, &err)) return fail("--hystrix-config: " + err);
+        cfg->app.breaker.apply(props);
+    }
+    for (const auto& kv : cfg->system_properties) {
+        if (kv.first.compare(0, 8, "hystrix.") == 0) cfg->app.breaker.apply_key(kv.first, kv.second);
+    }
+    return ParseOutcome::kRun;
+}
+
+Service::Service(ServiceConfig config) : config_(std::move(config)) {}
+
+Service::~Service() { stop(); }
+
+void Service::log(const char* level, const std::string& message) const {
+    if (config_.quiet && level[0] == 'I') return;
+    char stamp[32];
+    const time_t t = time(nullptr);
+    tm tmv;
+    localtime_r(&t, &tmv);
+    strftime(stamp, sizeof stamp, "%Y-%m-%d %H:%M:%S", &tmv);
+    std::fprintf(stderr, "%s %s [hola] %s\n", stamp, level, message.c_str());
+}
+
+bool Service::start(std::string* error) {
+    if (started_) return true;
+    const int64_t t_start = monotonic_ns();
+
+    if (const char* h = std::getenv("HOSTNAME")) config_.app.hostname = h;
+    std::string zipkin_url = config_.zipkin_url;
+    if (!config_.zipkin_url_given) {
+        if (const char* z = std::getenv("ZIPKIN_SERVER_URL")) zipkin_url = z;
+    }
+
+    // Configuration layers, highest ordinal first (core/config.h).
+    resolver_.reset(new ConfigResolver());
+    system_props_ = new SystemPropertySource();
+    for (const auto& kv : config_.system_properties) system_props_->set(kv.first, kv.second);
+    auto* conf_source = new ConfFileSource(system_props_);
+    if (config_.log_config_reads) {
+        conf_source->set_on_read([](const std::string* path) {
+            std::printf("%s\n", path ? path->c_str() : "null");  // Configuration.java:28
+            std::fflush(stdout);
+        });
+    }
+    resolver_->add_source(std::unique_ptr<ConfigSource>(system_props_));
+    resolver_->add_source(std::unique_ptr<ConfigSource>(new EnvironmentSource()));
+    if (!config_.deltaspike_properties.empty()) {
+        resolver_->add_source(std::unique_ptr<ConfigSource>(
+            new StaticPropertiesSource("META-INF/apache-deltaspike.properties", config_.deltaspike_properties)));
+    }
+    resolver_->add_source(std::unique_ptr<ConfigSource>(conf_source));
+
+    greeting_.reset(new GreetingService(resolver_.get(), config_.app.hostname,
+                                        [this](const std::string& m) { log("INFO", m); }));
+    tracer_.reset(new Tracer(zipkin_url, "hola", config_.zipkin_flush_ms));
+    if (!tracer_->error().empty()) log("WARN", tracer_->error() + " - tracing disabled");
+    dns_.reset(new Resolver());
+    for (const auto& kv : config_.static_hosts) {
+        in_addr addr;
+        inet_pton(AF_INET, kv.second.c_str(), &addr);
+        dns_->set_static(kv.first, addr.s_addr);
+    }
+    app_.reset(new HolaApp(config_.app, greeting_.get(), tracer_.get(), dns_.get()));
+    server_.reset(new Server(config_.server, app_.get()));
+    if (!server_->start(error)) {
+        server_.reset();
+        return false;
+    }
+    tracer_->start();
+    started_ = true;
+    char msg[256];
+    std::snprintf(msg, sizeof msg, "hola %s listening on %s:%u with %d thread(s), started in %.1f ms%s", HOLA_VERSION,
+                  config_.server.bind_address.c_str(), server_->port(), server_->threads(),
+                  static_cast<double>(monotonic_ns() - t_start) / 1e6, tracer_->enabled() ? ", tracing on" : "");
+    log("INFO", msg);
+    return true;
+}
+
+void Service::stop() {
+    if (!started_) return;
+    started_ = false;
+    server_->stop();
+    dns_->shutdown();
+    tracer_->stop();
+}
+
+}  // namespace hola

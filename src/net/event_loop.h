@@ -1,0 +1,95 @@
+// One epoll instance + timer heap + cross-thread mailbox, driven by exactly one thread.
+//
+// The reference borrows its I/O model from Undertow/XNIO (I/O threads + a worker pool,
+// /root/reference/pom.xml:122-129). The rebuild uses one event loop per core instead: a
+// connection lives on one loop for its whole life, handlers never block, and slow operations
+// (the downstream call, the metrics stream) are expressed as timers and non-blocking sockets on
+// the same loop. No locks are taken on the request path.
+#pragma once
+
+#include <sys/epoll.h>
+
+#include <atomic>
+#include <cstdint>
+#include <functional>
+#include <mutex>
+#include <queue>
+#include <unordered_map>
+#include <vector>
+
+namespace hola {
+
+class EventHandler {
+ public:
+    virtual ~EventHandler() = default;
+    virtual void on_events(uint32_t events) = 0;
+};
+
+int64_t monotonic_ns();
+int64_t realtime_us();
+
+class EventLoop {
+ public:
+    using TimerId = uint64_t;
+
+    EventLoop();
+    ~EventLoop();
+    EventLoop(const EventLoop&) = delete;
+    EventLoop& operator=(const EventLoop&) = delete;
+
+    // fd registration (loop thread only).
+    bool add(int fd, uint32_t events, EventHandler* handler);
+    bool modify(int fd, uint32_t events, EventHandler* handler);
+    void remove(int fd);
+
+    // Timers (loop thread only). The callback runs once, on the loop thread.
+    TimerId add_timer(int64_t deadline_ns, std::function<void()> cb);
+    void cancel_timer(TimerId id);
+
+    // Runs `fn` on the loop thread soon. Safe from any thread.
+    void post(std::function<void()> fn);
+
+    // Clock values sampled once per loop iteration.
+    int64_t now_ns() const { return now_ns_; }
+    int64_t now_unix_s() const { return now_unix_s_; }
+    int64_t now_unix_us() const { return now_unix_us_; }
+    void refresh_clock();
+
+    // Runs until stop() is called.
+    void run();
+    void stop();  // safe from any thread
+    bool stopping() const { return stop_.load(std::memory_order_relaxed); }
+
+    // Deferred deletion: objects whose handlers may still be referenced by the current batch of
+    // epoll events are parked here and destroyed at the end of the iteration.
+    void defer(std::function<void()> fn) { deferred_.push_back(std::move(fn)); }
+
+ private:
+    struct Timer {
+        int64_t deadline;
+        TimerId id;
+        bool operator>(const Timer& o) const { return deadline > o.deadline || (deadline == o.deadline && id > o.id); }
+    };
+
+    void drain_mailbox();
+    void run_timers();
+    int next_timeout_ms() const;
+
+    int epfd_ = -1;
+    int wake_fd_ = -1;
+    std::atomic<bool> stop_{false};
+    int64_t now_ns_ = 0;
+    int64_t now_unix_s_ = 0;
+    int64_t now_unix_us_ = 0;
+
+    std::priority_queue<Timer, std::vector<Timer>, std::greater<Timer>> timers_;
+    std::unordered_map<TimerId, std::function<void()>> timer_cbs_;
+    TimerId next_timer_id_ = 1;
+
+    std::mutex mailbox_mu_;
+    std::vector<std::function<void()>> mailbox_;
+    std::atomic<bool> mailbox_signalled_{false};
+    std::vector<std::function<void()>> deferred_;
+};
+
+}  // namespace hola

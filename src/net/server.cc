@@ -1,0 +1,534 @@
+#include "net/server.h"
+
+#include <arpa/inet.h>
+#include <fcntl.h>
+#include <netinet/in.h>
+#include <netinet/tcp.h>
+#include <pthread.h>
+#include <sched.h>
+#include <sys/socket.h>
+#include <unistd.h>
+
+#include <cerrno>
+#include <cstdio>
+#include <cstring>
+
+namespace hola {
+
+namespace {
+
+constexpr size_t kInitialInputCapacity = 4096;
+
+// Canned error responses produced by the server core itself (malformed or oversized heads).
+void append_core_error(std::string* out, int status, const char* reason, std::string_view date) {
+    out->append("HTTP/1.1 ");
+    out->append(std::to_string(status));
+    out->push_back(' ');
+    out->append(reason);
+    out->append("\r\nConnection: close\r\nContent-Length: 0\r\nDate: ");
+    out->append(date);
+    out->append("\r\n\r\n");
+}
+
+// Single-writer counter bump: a plain load/store pair instead of a locked read-modify-write.
+inline void bump(std::atomic<uint64_t>& counter) {
+    counter.store(counter.load(std::memory_order_relaxed) + 1, std::memory_order_relaxed);
+}
+
+}  // namespace
+
+bool set_nonblocking(int fd) {
+    const int flags = fcntl(fd, F_GETFL, 0);
+    return flags >= 0 && fcntl(fd, F_SETFL, flags | O_NONBLOCK) == 0;
+}
+
+void set_nodelay(int fd) {
+    const int one = 1;
+    setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Connection
+
+Connection::~Connection() {
+    if (fd_ >= 0) close(fd_);
+}
+
+void Connection::start(int fd) {
+    fd_ = fd;
+    if (!in_) {
+        in_.reset(new char[kInitialInputCapacity]);
+        in_cap_ = kInitialInputCapacity;
+    }
+    in_len_ = in_pos_ = 0;
+    out_.clear();
+    out_sent_ = 0;
+    want_write_ = close_after_write_ = deferred_ = streaming_ = peer_closed_ = in_process_ = false;
+    discard_remaining_ = 0;
+    discard_chunked_.reset();
+    last_active_ns_ = worker_->loop().now_ns();
+    registered_events_ = EPOLLIN | EPOLLRDHUP;
+    if (!worker_->loop().add(fd_, registered_events_, this)) close_now();
+}
+
+void Connection::close_now() {
+    if (fd_ < 0) return;
+    const ConnRef old = ref();
+    const bool notify = deferred_ || streaming_;
+    worker_->loop().remove(fd_);
+    close(fd_);
+    fd_ = -1;
+    ++generation_;
+    deferred_ = streaming_ = false;
+    if (in_cap_ > kInitialInputCapacity * 4) {  // do not let one large request pin memory
+        in_.reset();
+        in_cap_ = 0;
+    }
+    if (out_.capacity() > 65536) std::string().swap(out_);
+    out_.clear();
+    if (notify) worker_->app_->on_connection_closed(*worker_, old);
+    worker_->release(this);
+}
+
+void Connection::update_interest() {
+    if (fd_ < 0) return;
+    uint32_t ev = EPOLLRDHUP;
+    if (want_write_) ev |= EPOLLOUT;
+    bool can_read = !want_write_ || streaming_;
+    if (deferred_ && in_len_ >= worker_->options().max_header_bytes) can_read = false;
+    if (peer_closed_) can_read = false;
+    if (can_read) ev |= EPOLLIN;
+    if (peer_closed_) ev &= ~static_cast<uint32_t>(EPOLLRDHUP);
+    if (ev == registered_events_) return;
+    registered_events_ = ev;
+    worker_->loop().modify(fd_, ev, this);
+}
+
+void Connection::on_events(uint32_t events) {
+    if (fd_ < 0) return;  // closed earlier in this batch of events
+    if (events & EPOLLERR) {
+        close_now();
+        return;
+    }
+    if (events & EPOLLOUT) {
+        flush();
+        if (fd_ < 0) return;
+    }
+    if (!(events & (EPOLLIN | EPOLLHUP | EPOLLRDHUP))) return;
+    if (peer_closed_) {
+        if (events & EPOLLHUP) close_now();
+        return;
+    }
+    last_active_ns_ = worker_->loop().now_ns();
+    const size_t max_cap = worker_->options().max_header_bytes + kInitialInputCapacity;
+    while (fd_ >= 0) {
+        if (in_len_ == in_cap_) {
+            if (in_pos_ > 0) {
+                std::memmove(in_.get(), in_.get() + in_pos_, in_len_ - in_pos_);
+                in_len_ -= in_pos_;
+                in_pos_ = 0;
+            } else if (in_cap_ < max_cap) {
+                const size_t new_cap = std::min(max_cap, in_cap_ * 2);
+                std::unique_ptr<char[]> bigger(new char[new_cap]);
+                std::memcpy(bigger.get(), in_.get(), in_len_);
+                in_ = std::move(bigger);
+                in_cap_ = new_cap;
+            } else {
+                // Full and nothing can be consumed (deferred request with a greedy pipeliner).
+                update_interest();
+                return;
+            }
+        }
+        const size_t space = in_cap_ - in_len_;
+        const ssize_t n = recv(fd_, in_.get() + in_len_, space, 0);
+        if (n > 0) {
+            in_len_ += static_cast<size_t>(n);
+            process_input();
+            if (static_cast<size_t>(n) < space) break;  // socket drained
+            continue;
+        }
+        if (n == 0) {
+            peer_closed_ = true;
+            if (streaming_ || (!deferred_ && out_sent_ >= out_.size())) {
+                close_now();
+            } else {
+                close_after_write_ = true;  // finish what is owed, then close
+                update_interest();
+            }
+            return;
+        }
+        if (errno == EINTR) continue;
+        if (errno == EAGAIN || errno == EWOULDBLOCK) break;
+        close_now();
+        return;
+    }
+}
+
+bool Connection::discard_body_bytes() {
+    const size_t avail = in_len_ - in_pos_;
+    if (discard_chunked_) {
+        const size_t used = discard_chunked_->feed(in_.get() + in_pos_, avail, nullptr);
+        in_pos_ += used;
+        if (discard_chunked_->failed()) {
+            discard_chunked_.reset();
+            close_after_write_ = true;
+            return false;
+        }
+        if (!discard_chunked_->done()) return false;
+        discard_chunked_.reset();
+        return true;
+    }
+    const size_t take = static_cast<size_t>(std::min<int64_t>(discard_remaining_, static_cast<int64_t>(avail)));
+    in_pos_ += take;
+    discard_remaining_ -= static_cast<int64_t>(take);
+    return discard_remaining_ == 0;
+}
+
+void Connection::process_input() {
+    if (in_process_) return;
+    in_process_ = true;
+    while (fd_ >= 0 && !deferred_ && !streaming_ && !close_after_write_) {
+        if ((discard_remaining_ > 0 || discard_chunked_) && !discard_body_bytes()) break;
+        if (in_pos_ >= in_len_) break;
+        RequestHead head;
+        const ParseStatus st = parse_request_head(in_.get() + in_pos_, in_len_ - in_pos_, &head);
+        if (st == ParseStatus::kIncomplete) {
+            if (in_len_ - in_pos_ >= worker_->options().max_header_bytes) {
+                bump(worker_->stats_.bad_requests);
+                append_core_error(&out_, 431, "Request Header Fields Too Large", worker_->http_date());
+                close_after_write_ = true;
+            }
+            break;
+        }
+        if (st == ParseStatus::kBad) {
+            bump(worker_->stats_.bad_requests);
+            append_core_error(&out_, 400, "Bad Request", worker_->http_date());
+            close_after_write_ = true;
+            break;
+        }
+        in_pos_ += head.head_len;
+        if (head.chunked) {
+            discard_chunked_.reset(new ChunkedDecoder());
+        } else if (head.content_length > 0) {
+            discard_remaining_ = head.content_length;
+        }
+        if (!head.keep_alive || worker_->draining()) close_after_write_ = true;
+        if (head.expect_continue && (head.chunked || head.content_length > 0)) close_after_write_ = true;
+        bump(worker_->stats_.requests);
+        const Disposition d = worker_->app_->handle(*worker_, *this, head);
+        if (d == Disposition::kDeferred) {
+            deferred_ = true;
+        } else if (d == Disposition::kStream) {
+            streaming_ = true;
+        }
+    }
+    if (fd_ >= 0) {
+        if (in_pos_ >= in_len_) {
+            in_pos_ = in_len_ = 0;
+        } else if (in_pos_ > 0 && in_pos_ >= in_cap_ / 2) {
+            std::memmove(in_.get(), in_.get() + in_pos_, in_len_ - in_pos_);
+            in_len_ -= in_pos_;
+            in_pos_ = 0;
+        }
+    }
+    in_process_ = false;
+    flush();
+}
+
+void Connection::flush() {
+    if (fd_ < 0) return;
+    while (out_sent_ < out_.size()) {
+        const ssize_t n = send(fd_, out_.data() + out_sent_, out_.size() - out_sent_, MSG_NOSIGNAL);
+        if (n > 0) {
+            out_sent_ += static_cast<size_t>(n);
+            continue;
+        }
+        if (n < 0 && errno == EINTR) continue;
+        if (n < 0 && (errno == EAGAIN || errno == EWOULDBLOCK)) {
+            want_write_ = true;
+            update_interest();
+            return;
+        }
+        close_now();
+        return;
+    }
+    out_.clear();
+    out_sent_ = 0;
+    want_write_ = false;
+    if (close_after_write_ && !deferred_) {
+        close_now();
+        return;
+    }
+    update_interest();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Worker
+
+Worker::Worker(int id, const ServerOptions& options, Application* app) : id_(id), options_(options), app_(app) {}
+
+Worker::~Worker() {
+    if (listen_fd_ >= 0) close(listen_fd_);
+}
+
+std::string_view Worker::http_date() {
+    const int64_t s = loop_.now_unix_s();
+    if (s != date_second_) {
+        date_second_ = s;
+        format_http_date(s, date_);
+    }
+    return std::string_view(date_, 29);
+}
+
+bool Worker::open_listener(std::string* error) {
+    const int fd = socket(AF_INET, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
+    if (fd < 0) {
+        *error = std::string("socket: ") + std::strerror(errno);
+        return false;
+    }
+    const int one = 1;
+    setsockopt(fd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
+    if (options_.reuse_port) setsockopt(fd, SOL_SOCKET, SO_REUSEPORT, &one, sizeof one);
+    sockaddr_in addr{};
+    addr.sin_family = AF_INET;
+    addr.sin_port = htons(options_.port);
+    if (inet_pton(AF_INET, options_.bind_address.c_str(), &addr.sin_addr) != 1) {
+        *error = "bad bind address: " + options_.bind_address;
+        close(fd);
+        return false;
+    }
+    if (bind(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) != 0) {
+        *error = "bind " + options_.bind_address + ":" + std::to_string(options_.port) + ": " + std::strerror(errno);
+        close(fd);
+        return false;
+    }
+    if (listen(fd, options_.backlog) != 0) {
+        *error = std::string("listen: ") + std::strerror(errno);
+        close(fd);
+        return false;
+    }
+    listen_fd_ = fd;
+    return true;
+}
+
+void Worker::on_events(uint32_t /*events*/) {
+    // Listening socket readable: accept until the queue is empty.
+    while (listen_fd_ >= 0) {
+        const int fd = accept4(listen_fd_, nullptr, nullptr, SOCK_NONBLOCK | SOCK_CLOEXEC);
+        if (fd < 0) {
+            if (errno == EINTR) continue;
+            if (errno == EMFILE || errno == ENFILE) std::fprintf(stderr, "hola: accept: %s\n", std::strerror(errno));
+            return;
+        }
+        set_nodelay(fd);
+        if (peers_ && peers_->size() > 1) {
+            Worker* target = (*peers_)[rr_next_++ % peers_->size()];
+            if (target != this) {
+                target->loop().post([target, fd] { target->adopt(fd); });
+                continue;
+            }
+        }
+        adopt(fd);
+    }
+}
+
+void Worker::adopt(int fd) {
+    if (draining_) {
+        close(fd);
+        return;
+    }
+    Connection* c;
+    if (!free_.empty()) {
+        c = conns_[free_.back()].get();
+        free_.pop_back();
+    } else {
+        conns_.emplace_back(new Connection(this, static_cast<uint32_t>(conns_.size())));
+        c = conns_.back().get();
+    }
+    ++open_count_;
+    stats_.connections_accepted.fetch_add(1, std::memory_order_relaxed);
+    stats_.connections_open.fetch_add(1, std::memory_order_relaxed);
+    c->start(fd);
+}
+
+void Worker::release(Connection* c) {
+    free_.push_back(c->index_);
+    --open_count_;
+    stats_.connections_open.fetch_sub(1, std::memory_order_relaxed);
+    if (draining_ && open_count_ == 0) loop_.stop();
+}
+
+Connection* Worker::lookup(ConnRef ref) {
+    if (ref.index >= conns_.size()) return nullptr;
+    Connection* c = conns_[ref.index].get();
+    if (c->fd_ < 0 || c->generation_ != ref.generation) return nullptr;
+    return c;
+}
+
+bool Worker::complete(ConnRef ref, std::string_view response, bool close_after) {
+    Connection* c = lookup(ref);
+    if (!c || !c->deferred_) return false;
+    c->deferred_ = false;
+    c->out_.append(response);
+    if (close_after || c->peer_closed_ || draining_) c->close_after_write_ = true;
+    c->process_input();  // resumes parsing of pipelined requests, then flushes
+    return true;
+}
+
+bool Worker::stream_write(ConnRef ref, std::string_view bytes) {
+    Connection* c = lookup(ref);
+    if (!c || !c->streaming_) return false;
+    if (c->out_.size() - c->out_sent_ > (4u << 20)) {  // reader is not keeping up
+        c->close_now();
+        return false;
+    }
+    c->out_.append(bytes);
+    c->flush();
+    return c->fd_ >= 0;
+}
+
+void Worker::end_stream(ConnRef ref) {
+    Connection* c = lookup(ref);
+    if (!c || !c->streaming_) return;
+    c->streaming_ = false;  // no close notification for an orderly end
+    c->close_after_write_ = true;
+    c->flush();
+}
+
+void Worker::sweep_idle() {
+    const int64_t limit = static_cast<int64_t>(options_.idle_timeout_ms) * 1000000;
+    const int64_t now = loop_.now_ns();
+    for (auto& c : conns_) {
+        if (c->fd_ < 0 || c->deferred_ || c->streaming_) continue;
+        if (c->out_sent_ < c->out_.size()) continue;
+        if (now - c->last_active_ns_ > limit) c->close_now();
+    }
+    if (!draining_) {
+        loop_.add_timer(now + limit / 2 + 1000000, [this] { sweep_idle(); });
+    }
+}
+
+void Worker::begin_drain() {
+    if (draining_) return;
+    draining_ = true;
+    if (listen_fd_ >= 0) {
+        loop_.remove(listen_fd_);
+        close(listen_fd_);
+        listen_fd_ = -1;
+    }
+    app_->on_worker_stop(*this);
+    for (auto& c : conns_) {
+        if (c->fd_ < 0) continue;
+        if (c->streaming_) {
+            c->close_now();
+        } else if (!c->deferred_ && c->out_sent_ >= c->out_.size()) {
+            c->close_now();  // idle keep-alive connection
+        } else {
+            c->close_after_write_ = true;
+        }
+    }
+    if (open_count_ == 0) {
+        loop_.stop();
+        return;
+    }
+    loop_.add_timer(loop_.now_ns() + static_cast<int64_t>(options_.shutdown_grace_ms) * 1000000,
+                    [this] { loop_.stop(); });
+}
+
+void Worker::thread_main() {
+    if (!options_.cpu_affinity.empty()) {
+        const int cpu = options_.cpu_affinity[static_cast<size_t>(id_) % options_.cpu_affinity.size()];
+        cpu_set_t set;
+        CPU_ZERO(&set);
+        CPU_SET(cpu, &set);
+        pthread_setaffinity_np(pthread_self(), sizeof set, &set);
+    }
+    char name[16];
+    std::snprintf(name, sizeof name, "hola-io-%d", id_);
+    pthread_setname_np(pthread_self(), name);
+    loop_.refresh_clock();
+    app_->on_worker_start(*this);
+    if (listen_fd_ >= 0) loop_.add(listen_fd_, EPOLLIN, this);
+    if (options_.idle_timeout_ms > 0) {
+        loop_.add_timer(loop_.now_ns() + static_cast<int64_t>(options_.idle_timeout_ms) * 500000,
+                        [this] { sweep_idle(); });
+    }
+    loop_.run();
+    // Whatever is still open after the grace period goes down with the loop.
+    for (auto& c : conns_) {
+        if (c->fd_ >= 0) {
+            close(c->fd_);
+            c->fd_ = -1;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Server
+
+Server::Server(ServerOptions options, Application* app) : options_(std::move(options)), app_(app) {}
+
+Server::~Server() { stop(); }
+
+bool Server::start(std::string* error) {
+    int n = options_.threads;
+    if (n <= 0) {
+        cpu_set_t set;
+        CPU_ZERO(&set);
+        n = sched_getaffinity(0, sizeof set, &set) == 0 ? CPU_COUNT(&set) : 1;
+        if (n <= 0) n = 1;
+    }
+    options_.threads = n;
+    for (int i = 0; i < n; ++i) {
+        workers_.emplace_back(new Worker(i, options_, app_));
+        worker_ptrs_.push_back(workers_.back().get());
+    }
+    for (int i = 0; i < n; ++i) {
+        Worker& w = *workers_[static_cast<size_t>(i)];
+        if (!options_.reuse_port && i > 0) break;  // single acceptor
+        if (!w.open_listener(error)) {
+            workers_.clear();
+            worker_ptrs_.clear();
+            return false;
+        }
+        if (i == 0) {
+            sockaddr_in addr{};
+            socklen_t len = sizeof addr;
+            getsockname(w.listen_fd_, reinterpret_cast<sockaddr*>(&addr), &len);
+            bound_port_ = ntohs(addr.sin_port);
+            options_.port = bound_port_;  // later listeners join the same (possibly ephemeral) port
+        }
+    }
+    if (!options_.reuse_port) workers_[0]->peers_ = &worker_ptrs_;
+    for (auto& w : workers_) {
+        Worker* wp = w.get();
+        wp->thread_ = std::thread([wp] { wp->thread_main(); });
+    }
+    started_ = true;
+    return true;
+}
+
+void Server::stop() {
+    if (!started_) return;
+    started_ = false;
+    for (auto& w : workers_) {
+        Worker* wp = w.get();
+        wp->loop().post([wp] { wp->begin_drain(); });
+    }
+    for (auto& w : workers_) {
+        if (w->thread_.joinable()) w->thread_.join();
+    }
+}
+
+ServerStats Server::stats() const {
+    ServerStats s;
+    for (const auto& w : workers_) {
+        s.connections_accepted += w->stats_.connections_accepted.load(std::memory_order_relaxed);
+        s.connections_open += w->stats_.connections_open.load(std::memory_order_relaxed);
+        s.requests += w->stats_.requests.load(std::memory_order_relaxed);
+        s.bad_requests += w->stats_.bad_requests.load(std::memory_order_relaxed);
+    }
+    return s;
+}
+
+}  // namespace hola

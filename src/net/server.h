@@ -1,0 +1,219 @@
+// HTTP/1.1 server core: one Worker per thread, each with its own event loop, its own listening
+// socket (SO_REUSEPORT) or a share of a round-robin acceptor, and its own pool of connections.
+//
+// Replaces the Undertow listener the reference gets from WildFly Swarm on :8080
+// (/root/reference/Readme.md:16, /root/reference/Dockerfile:8, /root/reference/pom.xml:74).
+//
+// Request life cycle on a worker thread:
+//   recv -> parse_request_head (zero copy) -> Application::handle -> bytes appended to the
+//   connection's output buffer -> one send() per batch of pipelined requests.
+// A handler may instead *defer* (answer later from a timer or another socket's callback on the
+// same loop - used for the downstream call) or turn the connection into a *stream* (used for
+// the server-sent-events metrics feed). While a request is deferred the connection stops
+// parsing, so pipelined responses always go out in request order.
+#pragma once
+
+#include <atomic>
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <string_view>
+#include <thread>
+#include <vector>
+
+#include "core/http.h"
+#include "net/event_loop.h"
+
+namespace hola {
+
+class Worker;
+class Connection;
+
+enum class Disposition : uint8_t {
+    kDone,      // a complete response was appended to conn.out()
+    kDeferred,  // the handler will call Worker::complete() later
+    kStream,    // the handler took over the connection for streaming
+};
+
+// Stable handle to a connection that may have gone away in the meantime.
+struct ConnRef {
+    uint32_t index = 0;
+    uint32_t generation = 0;
+};
+
+class Application {
+ public:
+    virtual ~Application() = default;
+    // Called once on each worker thread before it starts serving.
+    virtual void on_worker_start(Worker& /*worker*/) {}
+    // Called once on each worker thread when it is shutting down.
+    virtual void on_worker_stop(Worker& /*worker*/) {}
+    virtual Disposition handle(Worker& worker, Connection& conn, const RequestHead& request) = 0;
+    // A deferred or streaming connection was closed by the peer (or by shutdown).
+    virtual void on_connection_closed(Worker& /*worker*/, ConnRef /*ref*/) {}
+};
+
+class Connection final : public EventHandler {
+ public:
+    explicit Connection(Worker* worker, uint32_t index) : worker_(worker), index_(index) {}
+    ~Connection() override;
+
+    void on_events(uint32_t events) override;
+
+    std::string& out() { return out_; }
+    // The response being appended is the last one on this connection.
+    void close_after_write() { close_after_write_ = true; }
+    ConnRef ref() const { return ConnRef{index_, generation_}; }
+    bool open() const { return fd_ >= 0; }
+    // True once the response being built must be the last one (client asked for close, or the
+    // server is shutting down); handlers then send "Connection: close".
+    bool closing() const { return close_after_write_; }
+
+ private:
+    friend class Worker;
+    void start(int fd);
+    void close_now();
+    void process_input();
+    void flush();
+    void update_interest();
+    bool discard_body_bytes();
+
+    Worker* worker_;
+    const uint32_t index_;
+    uint32_t generation_ = 0;
+    int fd_ = -1;
+
+    std::unique_ptr<char[]> in_;
+    size_t in_cap_ = 0;
+    size_t in_len_ = 0;
+    size_t in_pos_ = 0;
+
+    std::string out_;
+    size_t out_sent_ = 0;
+
+    bool want_write_ = false;
+    bool close_after_write_ = false;
+    bool deferred_ = false;
+    bool streaming_ = false;
+    bool peer_closed_ = false;
+    bool in_process_ = false;
+    int64_t discard_remaining_ = 0;
+    std::unique_ptr<ChunkedDecoder> discard_chunked_;
+    uint32_t registered_events_ = 0;
+    int64_t last_active_ns_ = 0;
+};
+
+struct ServerOptions {
+    std::string bind_address = "0.0.0.0";
+    uint16_t port = 8080;
+    int threads = 0;                  // 0: one per available CPU
+    int backlog = 1024;
+    size_t max_header_bytes = 65536;  // request line + headers
+    bool reuse_port = true;           // false: worker 0 accepts and deals connections round-robin
+    std::vector<int> cpu_affinity;    // optional: worker i is pinned to cpu_affinity[i % size]
+    int shutdown_grace_ms = 5000;
+    int idle_timeout_ms = 0;          // 0: never close idle keep-alive connections
+};
+
+// Counters are kept per worker (single writer, so no cache line is shared between cores on
+// the request path) and summed on demand.
+struct WorkerStats {
+    std::atomic<uint64_t> connections_accepted{0};
+    std::atomic<uint64_t> connections_open{0};
+    std::atomic<uint64_t> requests{0};
+    std::atomic<uint64_t> bad_requests{0};
+};
+
+struct ServerStats {
+    uint64_t connections_accepted = 0;
+    uint64_t connections_open = 0;
+    uint64_t requests = 0;
+    uint64_t bad_requests = 0;
+};
+
+class Worker final : public EventHandler {
+ public:
+    Worker(int id, const ServerOptions& options, Application* app);
+    ~Worker() override;
+
+    int id() const { return id_; }
+    EventLoop& loop() { return loop_; }
+    const ServerOptions& options() const { return options_; }
+    bool draining() const { return draining_; }
+
+    // 29-byte HTTP date for the current second (cached).
+    std::string_view http_date();
+
+    // Completes a deferred request: appends `response` and resumes the connection. Returns
+    // false when the connection no longer exists (the response is dropped).
+    bool complete(ConnRef ref, std::string_view response, bool close_after);
+    // Writes to a streaming connection; false when it is gone. end_stream() closes it once the
+    // buffered bytes are out.
+    bool stream_write(ConnRef ref, std::string_view bytes);
+    void end_stream(ConnRef ref);
+    Connection* lookup(ConnRef ref);
+
+    // Per-worker slot for application state (owned by the application).
+    void set_app_state(void* p) { app_state_ = p; }
+    void* app_state() const { return app_state_; }
+
+    // Listening-socket events.
+    void on_events(uint32_t events) override;
+
+ private:
+    friend class Server;
+    friend class Connection;
+    bool open_listener(std::string* error);
+    void adopt(int fd);  // loop thread
+    void release(Connection* c);
+    void begin_drain();
+    void thread_main();
+    void sweep_idle();
+
+    const int id_;
+    const ServerOptions& options_;
+    Application* app_;
+    alignas(64) WorkerStats stats_;
+    EventLoop loop_;
+    int listen_fd_ = -1;
+    bool draining_ = false;
+    std::vector<std::unique_ptr<Connection>> conns_;
+    std::vector<uint32_t> free_;
+    size_t open_count_ = 0;
+    std::vector<Worker*>* peers_ = nullptr;  // round-robin mode: all workers
+    size_t rr_next_ = 0;
+    int64_t date_second_ = -1;
+    char date_[29];
+    void* app_state_ = nullptr;
+    std::thread thread_;
+};
+
+class Server {
+ public:
+    Server(ServerOptions options, Application* app);
+    ~Server();
+
+    // Binds the listeners and starts the worker threads. Returns false with *error set when a
+    // socket cannot be opened.
+    bool start(std::string* error);
+    // Stops accepting, lets in-flight responses finish (bounded by shutdown_grace_ms), joins.
+    void stop();
+    uint16_t port() const { return bound_port_; }
+    int threads() const { return static_cast<int>(workers_.size()); }
+    ServerStats stats() const;
+    Worker& worker(int i) { return *workers_[static_cast<size_t>(i)]; }
+
+ private:
+    ServerOptions options_;
+    Application* app_;
+    std::vector<std::unique_ptr<Worker>> workers_;
+    std::vector<Worker*> worker_ptrs_;
+    uint16_t bound_port_ = 0;
+    bool started_ = false;
+};
+
+// Small helpers shared with the outbound client.
+bool set_nonblocking(int fd);
+void set_nodelay(int fd);
+
+}  // namespace hola
