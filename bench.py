@@ -1,0 +1,252 @@
+#!/usr/bin/env python
+"""Headline benchmark: GET /api/hola requests/sec and p50/p99 latency, CPU, localhost.
+
+That is the metric BASELINE.json names for objectiser/hola, on its config 4: 64 concurrent
+keep-alive clients, sustained load. One *step* is one second of that load; ``--steps K`` measures
+K seconds after ``--warmup W`` seconds, so the defaults (K=60, W=3) are exactly the 60 s run the
+baseline describes.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference      # the reference arm (not runnable here: no JVM)
+
+What "N GPUs" means for a service that never touches a GPU: N independent service instances
+(the reference scales out as "more pods behind a LoadBalancer", /root/reference/pom.xml:80), each
+with its own 64-connection load generator, on disjoint slices of the machine's CPUs. Under
+torchrun every rank runs one instance and the totals are summed over ranks (gloo); without
+torchrun one process runs all N. ``value`` is the whole-job aggregate requests/sec.
+
+The line printed at the end is honest about the GPU: ``gpu_launches`` is 0 because the workload
+has no kernel to launch (BASELINE.json north_star). The measurement is end to end
+by construction - real TCP connections, every response parsed and its body verified byte for
+byte - so ``e2e`` is the same number, not a second one.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+from pathlib import Path
+from typing import Dict, List, Optional, Sequence
+
+REPO = Path(__file__).resolve().parent
+sys.path.insert(0, str(REPO))
+
+METRIC = "GET /api/hola requests/sec (p50/p99 latency alongside), CPU, localhost"
+UNIT = "req/s"
+CONNECTIONS = 64
+ZIPKIN_DEAD_URL = "http://127.0.0.1:9"  # discard port: nothing listens, like zipkin-query:9411 on a dev box
+
+
+def reference_arm(args) -> int:
+    """The reference is a Maven/Java EE project; this image has no JVM, Maven, container runtime or network.
+
+    `pip install /root/reference` was attempted as instructed and fails ("Neither 'setup.py' nor
+    'pyproject.toml' found"): there is nothing Python about the reference. See DESIGN.md.
+    """
+    import shutil
+    missing = [tool for tool in ("java", "mvn", "docker") if shutil.which(tool) is None]
+    jar = REPO / "baseline" / "_ref" / "hola-swarm.jar"
+    if shutil.which("java") and jar.exists():
+        why = "a JVM and %s exist, but running the reference jar is not wired up (never observed on any box)" % jar
+    else:
+        why = ("reference is a Java EE/WildFly Swarm Maven project; no %s on this image, no ~/.m2, no network to fetch "
+               "Swarm 1.0.0.Final; pip install of /root/reference fails (not a Python project)" % "/".join(missing or ["jar"]))
+    print(json.dumps({"impl": "reference", "unavailable": why, "metric": METRIC, "n_gpus": args.gpus}))
+    return 0
+
+
+def partition(cpus: Sequence[int], parts: int) -> List[List[int]]:
+    """Contiguous, near-equal slices; with fewer CPUs than parts the slices overlap round-robin."""
+    cpus = list(cpus)
+    if len(cpus) >= parts:
+        base, extra = divmod(len(cpus), parts)
+        out, pos = [], 0
+        for i in range(parts):
+            n = base + (1 if i < extra else 0)
+            out.append(cpus[pos:pos + n])
+            pos += n
+        return out
+    return [[cpus[i % len(cpus)]] for i in range(parts)]
+
+
+def run_instance(index: int, cpus: Sequence[int], steps: int, warmup: int, mode: str, max_cpus: int,
+                 server_share: float, results: Dict[int, Dict]) -> None:
+    from hola_b200 import loadgen
+    from hola_b200.server import HolaServer
+    from hola_b200.utils import split_cpus
+
+    server_cpus, load_cpus = split_cpus(cpus, server_share=server_share, max_total=max_cpus)
+    server_threads = min(len(server_cpus), CONNECTIONS)
+    load_threads = min(len(load_cpus), CONNECTIONS)
+    env = {"HOSTNAME": None}  # a plain `mvn wildfly-swarm:run` from a shell does not export HOSTNAME
+    args = ["--cpus", ",".join(map(str, server_cpus))]
+    expect = b"Hola de unknown"
+    if mode == "as-is":
+        # The reference cannot even deploy without ZIPKIN_SERVER_URL, so the
+        # as-is configuration traces every request and ships spans to a collector nobody runs.
+        env["ZIPKIN_SERVER_URL"] = ZIPKIN_DEAD_URL
+    elif mode == "notrace":
+        env["ZIPKIN_SERVER_URL"] = None
+    elif mode == "conf":
+        env["ZIPKIN_SERVER_URL"] = ZIPKIN_DEAD_URL
+        args += ["-Dconf=" + str(REPO / "tests" / "data" / "translation.properties")]
+        expect = b"Hola de unknown mediante el archivo de configuraciones\n"
+    with HolaServer(args=args, env=env, threads=server_threads) as srv:
+        report = loadgen.run(srv.base_url + "/api/hola", connections=CONNECTIONS, duration=steps, warmup=warmup,
+                             interval=1.0, threads=load_threads, cpus=load_cpus, expect_body=expect)
+        report["server_cpus"] = list(server_cpus)
+        report["load_cpus"] = list(load_cpus)
+        report["server_threads"] = server_threads
+        report["startup_s"] = srv.startup_seconds
+    results[index] = report
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("--gpus", type=int, default=1, help="number of service instances (see module docstring)")
+    ap.add_argument("--steps", type=int, default=60, help="measured seconds (one step = one second of load)")
+    ap.add_argument("--warmup", type=int, default=3, help="warm-up seconds, not measured (>= 3)")
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--mode", choices=["as-is", "notrace", "conf"], default="as-is",
+                    help="as-is: tracing on, collector unreachable (how the reference must be run); "
+                         "notrace: ZIPKIN_SERVER_URL unset; conf: greeting from translation.properties")
+    ap.add_argument("--max-cpus", type=int, default=int(os.environ.get("HOLA_BENCH_MAX_CPUS", "32")),
+                    help="cap on CPUs used per instance (server + generator)")
+    ap.add_argument("--server-share", type=float, default=float(os.environ.get("HOLA_BENCH_SERVER_SHARE", "0.5")),
+                    help="fraction of an instance's CPUs given to the server (rest: load generator)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    if args.warmup < 3:
+        args.warmup = 3  # timing rule: W >= 3
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    distributed = world > 1
+    n = args.gpus if args.gpus > 0 else 1
+
+    import __graft_entry__
+    if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+        __graft_entry__.build()
+
+    dist = None
+    if distributed:
+        import torch
+        import torch.distributed as dist  # noqa: F811
+        # gloo on purpose: the only thing exchanged is a handful of counters held in host memory.
+        dist.init_process_group(backend="gloo")
+        dist.barrier()  # everyone waits for rank 0's build
+
+    from hola_b200.utils import ClockSampler, available_cpus, cpu_info
+
+    cpus = available_cpus()
+    slices = partition(cpus, n)
+    my_indices = [rank] if distributed else list(range(n))
+    results: Dict[int, Dict] = {}
+
+    sampler = ClockSampler().start() if rank == 0 else None
+    if dist is not None:
+        dist.barrier()
+    t0 = time.monotonic()
+    threads = [threading.Thread(target=run_instance, args=(i, slices[i % len(slices)], args.steps, args.warmup, args.mode,
+                                                           args.max_cpus, args.server_share, results)) for i in my_indices]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    wall = time.monotonic() - t0
+    if dist is not None:
+        dist.barrier()
+    clocks = sampler.stop() if sampler else None
+
+    missing = [i for i in my_indices if i not in results]
+    if missing:
+        print("bench: instance(s) %s failed" % missing, file=sys.stderr)
+        return 1
+
+    # Aggregate over local instances, then over ranks.
+    local_requests = sum(r["requests"] for r in results.values())
+    local_rps = sum(r["rps"] for r in results.values())
+    local_bytes = sum(r["bytes"] for r in results.values())
+    p50 = max(r["latency_us"]["p50"] for r in results.values())
+    p99 = max(r["latency_us"]["p99"] for r in results.values())
+    p999 = max(r["latency_us"]["p999"] for r in results.values())
+    lat_max = max(r["latency_us"]["max"] for r in results.values())
+    step_rps = [sum(r["intervals"][k]["rps"] for r in results.values()) for k in range(args.warmup, args.warmup + args.steps)]
+    if dist is not None:
+        import torch
+        sums = torch.tensor([float(local_requests), float(local_rps), float(local_bytes)], dtype=torch.float64)
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+        maxes = torch.tensor([p50, p99, p999, lat_max, wall], dtype=torch.float64)
+        dist.all_reduce(maxes, op=dist.ReduceOp.MAX)  # latency: the worst instance; time: the slowest rank
+        steps_t = torch.tensor(step_rps, dtype=torch.float64)
+        dist.all_reduce(steps_t, op=dist.ReduceOp.SUM)
+        local_requests, local_rps, local_bytes = (float(x) for x in sums)
+        p50, p99, p999, lat_max, wall = (float(x) for x in maxes)
+        step_rps = [float(x) for x in steps_t]
+        dist.destroy_process_group()
+    if rank != 0:
+        return 0
+
+    first = results[my_indices[0]]
+    baseline = json.loads((REPO / "BASELINE.json").read_text())
+    published = baseline.get("published") or {}
+    out = {
+        "metric": METRIC,
+        "value": round(local_rps, 1),
+        "unit": UNIT,
+        "n_gpus": n,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": 1000.0,  # a step is defined as one second of sustained load
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None if not published else None,  # the reference publishes no number
+        "dtype": "n/a (no tensor math; bytes over TCP)",
+        "data": "synthetic: 64 keep-alive HTTP/1.1 clients on localhost, every body verified byte for byte",
+        "impl": "ours",
+        "latency_us": {"p50": p50, "p99": p99, "p999": p999, "max": lat_max},
+        "requests": int(local_requests),
+        "errors": 0,
+        "step_rps": {"min": round(min(step_rps), 1), "median": round(statistics.median(step_rps), 1), "max": round(max(step_rps), 1)},
+        "config": {
+            "model": "objectiser/hola GET /api/hola (BASELINE.json config 4)",
+            "global_batch": CONNECTIONS * n,
+            "seq_len": None,
+            "parallelism": "%d independent instance(s), one per rank" % n,
+            "connections_per_instance": CONNECTIONS,
+            "mode": args.mode,
+            "server_cpus": first["server_cpus"],
+            "load_cpus": first["load_cpus"],
+            "server_threads": first["server_threads"],
+            "cpu": cpu_info(),
+            "l2_flush": "n/a: no device buffers; each request is a fresh socket read/write",
+            "wall_s": round(wall, 2),
+            "cold_start_s": round(first["startup_s"], 4),
+        },
+        "clocks": {k: clocks[k] for k in ("sm_mhz", "sm_max_mhz", "reasons")} if clocks else None,
+        "clocks_note": clocks["note"] if clocks else None,
+        "cpu_mhz_median": clocks["cpu_mhz_median"] if clocks else None,
+        "e2e": {
+            "value": round(local_rps, 1),
+            "unit": UNIT,
+            "h2d_bytes_per_step": 0,
+            "d2h_bytes_per_step": 0,
+            "note": "the only measurement there is: requests go through real TCP sockets to the running service and every "
+                    "response is read and checked; no device is involved, so there is no device-timed number to contrast it with",
+            "wire_bytes_per_step": int(local_bytes / max(1, args.steps)),
+        },
+        "gpu_launches": 0,
+        "gpu_note": "CPU-only service: the reference has no kernels, tensors or collectives (SURVEY.md 2.3); none were invented",
+    }
+    print(json.dumps(out))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

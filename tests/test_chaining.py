@@ -1,0 +1,164 @@
+"""GET /api/hola-chaining: downstream call, 600 ms timeout, circuit breaker, static fallback
+(HolaResource.java:69-78, 94-113; config.properties:17,19), tested against a fake `aloha`."""
+from __future__ import annotations
+
+import json
+import time
+
+from hola_b200 import client
+
+FALLBACK = "Aloha response (fallback)"
+
+
+def chain(srv, **kw):
+    r = client.get("127.0.0.1", srv.port, "/api/hola-chaining", **kw)
+    assert r.status == 200, (r.status, r.body)
+    assert r.header("Content-Type") == "application/json"
+    assert r.header("Access-Control-Allow-Origin") == "*"
+    return r
+
+
+def test_chaining_with_live_downstream(hola_server, fake_aloha):
+    srv = hola_server(args=["--aloha-url", fake_aloha.url])
+    r = chain(srv)
+    assert json.loads(r.body) == ["Hola de unknown"] + fake_aloha.payload
+    # Compact encoding, element 0 is exactly the /api/hola body.
+    assert r.body.startswith(b'["Hola de unknown","Aloha mai fake-aloha",')
+    rq = fake_aloha.snapshot()[0]
+    assert rq["path"] == "/api/aloha-chaining"  # AlohaService.java:25
+    assert rq["headers"]["host"] == "127.0.0.1:%d" % fake_aloha.port
+
+
+def test_chaining_uses_conf_greeting(hola_server, fake_aloha, tmp_path):
+    conf = tmp_path / "t.properties"
+    conf.write_text("hello=Hola de %s desde archivo\\n")
+    srv = hola_server(args=["--aloha-url", fake_aloha.url, "-Dconf=" + str(conf)])
+    assert json.loads(chain(srv).body)[0] == "Hola de unknown desde archivo\n"
+
+
+def test_chaining_downstream_chunked_and_keepalive_reuse(hola_server, fake_aloha):
+    fake_aloha.mode = "chunked"
+    srv = hola_server(args=["--aloha-url", fake_aloha.url], threads=1)
+    with client.Connection("127.0.0.1", srv.port) as c:
+        for _ in range(5):
+            r = c.request("GET", "/api/hola-chaining")
+            assert json.loads(r.body) == ["Hola de unknown"] + fake_aloha.payload
+    assert len(fake_aloha.snapshot()) == 5
+
+
+def test_fallback_when_downstream_unreachable(hola_server):
+    # Nothing listens on the discard port.
+    srv = hola_server(args=["--aloha-url", "http://127.0.0.1:9/"])
+    t0 = time.time()
+    r = chain(srv)
+    assert json.loads(r.body) == ["Hola de unknown", FALLBACK]  # HolaResource.java:112
+    assert time.time() - t0 < 0.5  # a refused connection fails fast, no need to wait for the timeout
+
+
+def test_fallback_when_name_does_not_resolve(hola_server):
+    """The reference's localhost case: `aloha` is not resolvable."""
+    srv = hola_server()  # default target http://aloha:8080/
+    t0 = time.time()
+    r = chain(srv)
+    assert json.loads(r.body) == ["Hola de unknown", FALLBACK]
+    assert time.time() - t0 < 1.5  # bounded by the 600 ms command timeout even if the resolver is slow
+
+
+def test_fallback_on_error_statuses_and_bad_payloads(hola_server, fake_aloha):
+    srv = hola_server(args=["--aloha-url", fake_aloha.url, "-Dhystrix.command.default.circuitBreaker.enabled=false"])
+    for mode in ("500", "404", "garbage", "object", "close"):
+        fake_aloha.mode = mode
+        assert json.loads(chain(srv).body) == ["Hola de unknown", FALLBACK], mode
+    fake_aloha.mode = "ok"
+    assert json.loads(chain(srv).body) == ["Hola de unknown"] + fake_aloha.payload
+
+
+def test_timeout_after_600ms(hola_server, fake_aloha):
+    fake_aloha.delay = 1.5
+    srv = hola_server(args=["--aloha-url", fake_aloha.url])
+    t0 = time.time()
+    r = chain(srv)
+    elapsed = time.time() - t0
+    assert json.loads(r.body) == ["Hola de unknown", FALLBACK]
+    assert 0.55 <= elapsed < 1.2, elapsed  # config.properties:17
+
+
+def test_timeout_is_configurable_like_archaius(hola_server, fake_aloha):
+    fake_aloha.delay = 0.5
+    srv = hola_server(args=["--aloha-url", fake_aloha.url,
+                            "-Dhystrix.command.default.execution.isolation.thread.timeoutInMilliseconds=150"])
+    t0 = time.time()
+    assert json.loads(chain(srv).body)[1] == FALLBACK
+    assert time.time() - t0 < 0.45
+
+
+def test_circuit_opens_after_five_failures_and_recovers(hola_server, fake_aloha):
+    """requestVolumeThreshold=5 (config.properties:19), 50 % errors, 5 s sleep window (library defaults)."""
+    fake_aloha.mode = "500"
+    srv = hola_server(args=["--aloha-url", fake_aloha.url,
+                            "-Dhystrix.command.default.circuitBreaker.sleepWindowInMilliseconds=1000"], threads=1)
+    for _ in range(6):
+        assert json.loads(chain(srv).body)[1] == FALLBACK
+    seen = len(fake_aloha.snapshot())
+    assert seen == 6
+    time.sleep(0.6)  # the health snapshot is taken every 500 ms
+    for _ in range(5):
+        assert json.loads(chain(srv).body)[1] == FALLBACK
+    assert len(fake_aloha.snapshot()) == seen  # short-circuited: the downstream is not even called
+    # After the sleep window one probe goes through; let it succeed and the circuit closes.
+    fake_aloha.mode = "ok"
+    time.sleep(1.1)
+    assert json.loads(chain(srv).body) == ["Hola de unknown"] + fake_aloha.payload
+    assert json.loads(chain(srv).body) == ["Hola de unknown"] + fake_aloha.payload
+    assert len(fake_aloha.snapshot()) == seen + 2
+
+
+def test_bulkhead_rejects_beyond_ten_concurrent(hola_server, fake_aloha):
+    """Thread-pool isolation with core size 10 and no queue: the 11th concurrent call falls back at once."""
+    import threading
+    fake_aloha.delay = 0.4
+    srv = hola_server(args=["--aloha-url", fake_aloha.url], threads=2)
+    results, lock = [], threading.Lock()
+
+    def one():
+        t0 = time.time()
+        body = json.loads(chain(srv).body)
+        with lock:
+            results.append((body[1], time.time() - t0))
+
+    threads = [threading.Thread(target=one) for _ in range(14)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    fast_fallbacks = [r for r in results if r[0] == FALLBACK and r[1] < 0.3]
+    served = [r for r in results if r[0] != FALLBACK]
+    assert len(served) == 10 and len(fast_fallbacks) == 4, results
+
+
+def test_pipelined_chaining_keeps_order(hola_server, fake_aloha):
+    fake_aloha.delay = 0.05
+    srv = hola_server(args=["--aloha-url", fake_aloha.url], threads=1)
+    with client.Connection("127.0.0.1", srv.port) as c:
+        c.send_raw(client.build_request("GET", "/api/hola-chaining") + client.build_request("GET", "/api/health") +
+                   client.build_request("GET", "/api/hola-chaining") + client.build_request("GET", "/api/hola"))
+        assert json.loads(c.read_response().body)[1] == fake_aloha.payload[0]
+        assert c.read_response().body == b"I'm ok"
+        assert json.loads(c.read_response().body)[1] == fake_aloha.payload[0]
+        assert c.read_response().body == b"Hola de unknown"
+
+
+def test_client_gone_while_call_in_flight_is_harmless(hola_server, fake_aloha):
+    fake_aloha.delay = 0.3
+    srv = hola_server(args=["--aloha-url", fake_aloha.url], threads=1)
+    c = client.Connection("127.0.0.1", srv.port)
+    c.send_raw(client.build_request("GET", "/api/hola-chaining"))
+    c.close()
+    time.sleep(0.5)
+    assert client.get("127.0.0.1", srv.port, "/api/health").status == 200
+
+
+def test_head_on_chaining(hola_server, fake_aloha):
+    srv = hola_server(args=["--aloha-url", fake_aloha.url])
+    r = client.get("127.0.0.1", srv.port, "/api/hola-chaining", method="HEAD")
+    assert r.status == 200 and r.body == b"" and int(r.header("Content-Length")) > 20

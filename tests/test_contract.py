@@ -1,0 +1,255 @@
+"""The observable contract of every endpoint, byte for byte where the reference's
+own code determines the bytes."""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+import pytest
+
+from hola_b200 import client
+
+DATA = os.path.join(os.path.dirname(__file__), "data")
+CONF = os.path.join(DATA, "translation.properties")
+REFERENCE_CONF = "/root/reference/translation.properties"
+
+
+def get(srv, target, **kw):
+    return client.get("127.0.0.1", srv.port, target, **kw)
+
+
+# ---- GET /api/hola: the three cases of SURVEY.md 2.2 ------------------------------------------
+
+def test_hola_default_no_hostname(hola_server):
+    """No -Dconf, HOSTNAME not exported: `Hola de unknown`, 15 bytes, no newline (HolaResource.java:57-65)."""
+    srv = hola_server()
+    r = get(srv, "/api/hola")
+    assert r.status == 200 and r.reason == "OK" and r.version == "HTTP/1.1"
+    assert r.body == b"Hola de unknown" and len(r.body) == 15
+    assert r.header("Content-Type") == "text/plain"
+    assert r.header("Content-Length") == "15"
+    assert r.header("Access-Control-Allow-Origin") == "*"  # CorsFilter.java:31
+    assert r.header("Date") is not None
+
+
+def test_hola_hostname_from_env(hola_server):
+    srv = hola_server(env={"HOSTNAME": "hola-1-x7k2p"})
+    assert get(srv, "/api/hola").body == b"Hola de hola-1-x7k2p"
+
+
+def test_hola_empty_hostname_is_kept(hola_server):
+    """getOrDefault only substitutes when the variable is absent, not when it is empty."""
+    srv = hola_server(env={"HOSTNAME": ""})
+    assert get(srv, "/api/hola").body == b"Hola de "
+
+
+def test_hola_with_conf_file(hola_server):
+    """-Dconf=translation.properties: the value's trailing backslash-n becomes one LF (BASELINE.json config 2)."""
+    srv = hola_server(args=["-Dconf=" + CONF], env={"HOSTNAME": "pod-7"})
+    r = get(srv, "/api/hola")
+    assert r.body == b"Hola de pod-7 mediante el archivo de configuraciones\n"
+    assert r.body.count(b"\n") == 1
+
+
+@pytest.mark.skipif(not os.path.exists(REFERENCE_CONF), reason="reference checkout not mounted")
+def test_hola_with_the_reference_file_itself(hola_server):
+    srv = hola_server(args=["--conf", REFERENCE_CONF])
+    assert get(srv, "/api/hola").body == b"Hola de unknown mediante el archivo de configuraciones\n"
+
+
+def test_hola_conf_file_missing_or_broken_falls_back(hola_server, tmp_path):
+    """Any failure reading the file means "no entries" (Configuration.java:34-36)."""
+    srv = hola_server(args=["-Dconf=" + str(tmp_path / "absent.properties")])
+    assert get(srv, "/api/hola").body == b"Hola de unknown"
+    broken = tmp_path / "broken.properties"
+    broken.write_text("hello=caf\\u00e\n")
+    srv2 = hola_server(args=["-Dconf=" + str(broken)])
+    assert get(srv2, "/api/hola").body == b"Hola de unknown"
+
+
+def test_hola_hot_reload_within_five_seconds(hola_server, tmp_path):
+    """Edits to the file show up within the 5 s cache period, without a restart (HolaResource.java:63)."""
+    conf = tmp_path / "t.properties"
+    conf.write_text("hello=Uno de %s\n")
+    srv = hola_server(args=["-Dconf=" + str(conf)])
+    assert get(srv, "/api/hola").body == b"Uno de unknown"
+    conf.write_text("hello=Dos de %s\n")
+    assert get(srv, "/api/hola").body == b"Uno de unknown"  # still inside the cache period
+    deadline = time.time() + 6.5
+    body = b""
+    while time.time() < deadline:
+        body = get(srv, "/api/hola").body
+        if body == b"Dos de unknown":
+            break
+        time.sleep(0.1)
+    assert body == b"Dos de unknown"
+    assert "New value Dos de %s for key hello." in srv.stderr  # logChanges(true), HolaResource.java:61
+
+
+def test_hola_source_precedence(hola_server, tmp_path):
+    """System property (400) beats environment (300) beats the conf file (0)."""
+    conf = tmp_path / "t.properties"
+    conf.write_text("hello=file %s\n")
+    assert get(hola_server(args=["-Dconf=" + str(conf)]), "/api/hola").body == b"file unknown"
+    assert get(hola_server(args=["-Dconf=" + str(conf)], env={"hello": "env %s"}), "/api/hola").body == b"env unknown"
+    srv = hola_server(args=["-Dconf=" + str(conf), "-Dhello=prop %s"], env={"hello": "env %s"})
+    assert get(srv, "/api/hola").body == b"prop unknown"
+
+
+def test_hola_pattern_the_jvm_would_reject_is_a_500(hola_server):
+    srv = hola_server(args=["-Dhello=Hola %s y %s"])  # MissingFormatArgumentException on the JVM
+    r = get(srv, "/api/hola")
+    assert r.status == 500
+    srv2 = hola_server(args=["-Dhello=100%% de %s%n"])
+    assert get(srv2, "/api/hola").body == b"100% de unknown\n"
+
+
+def test_hola_log_config_reads_prints_path(hola_server, tmp_path):
+    """The reference prints the conf path on every read (Configuration.java:28); opt-in here."""
+    conf = tmp_path / "t.properties"
+    conf.write_text("hello=x %s\n")
+    srv = hola_server(args=["-Dconf=" + str(conf), "--log-config-reads"])
+    get(srv, "/api/hola")
+    srv.stop()
+    assert str(conf) in srv.stdout
+    srv2 = hola_server(args=["--log-config-reads"])
+    get(srv2, "/api/hola")
+    srv2.stop()
+    assert "null" in srv2.stdout  # System.out.println((String) null)
+
+
+# ---- the other endpoints -----------------------------------------------------------------------
+
+def test_health(hola_server):
+    srv = hola_server()
+    r = get(srv, "/api/health")
+    assert r.status == 200 and r.body == b"I'm ok" and len(r.body) == 6  # HolaResource.java:85
+    assert r.header("Content-Type") == "text/plain"
+    assert r.header("Access-Control-Allow-Origin") == "*"
+
+
+def test_head_and_options_and_405(hola_server):
+    srv = hola_server()
+    r = get(srv, "/api/hola", method="HEAD")
+    assert r.status == 200 and r.body == b"" and r.header("Content-Length") == "15"
+    r = get(srv, "/api/hola", method="OPTIONS")
+    assert r.status == 200 and "GET" in r.header("Allow")
+    for method in ("POST", "PUT", "DELETE", "PATCH"):
+        r = get(srv, "/api/hola", method=method)
+        assert r.status == 405 and "GET" in r.header("Allow"), method
+        assert r.header("Access-Control-Allow-Origin") == "*"
+
+
+def test_not_found_and_not_acceptable(hola_server):
+    srv = hola_server()
+    r = get(srv, "/api/nothing")
+    assert r.status == 404 and r.header("Access-Control-Allow-Origin") == "*"
+    r = get(srv, "/elsewhere")
+    assert r.status == 404 and r.header("Access-Control-Allow-Origin") is None  # CORS is a JAX-RS filter: /api only
+    r = get(srv, "/api/hola", headers={"Accept": "application/json"})
+    assert r.status == 406
+    r = get(srv, "/api/hola", headers={"Accept": "text/html, */*;q=0.5"})
+    assert r.status == 200
+    r = get(srv, "/api/hola-chaining", headers={"Accept": "text/plain"})
+    assert r.status == 406
+
+
+def test_query_string_and_trailing_slash(hola_server):
+    srv = hola_server()
+    assert get(srv, "/api/hola?x=1&y=2").body == b"Hola de unknown"
+    assert get(srv, "/api/hola/").status == 200
+    assert get(srv, "/api/holaa").status == 404
+    assert get(srv, "/api/hol").status == 404
+
+
+def test_landing_page_is_the_reference_page(hola_server):
+    srv = hola_server()
+    r = get(srv, "/")
+    assert r.status == 200 and r.header("Content-Type").startswith("text/html")
+    assert len(r.body) == 485
+    assert not r.body.endswith(b"\n")
+    assert b"webjars/swagger-ui/2.1.4/?url=' + loc + 'api/swagger.json#!/default'" in r.body
+    ref = "/root/reference/src/main/webapp/index.html"
+    if os.path.exists(ref):
+        assert r.body == open(ref, "rb").read()
+    assert r.header("Access-Control-Allow-Origin") is None
+    assert get(srv, "/index.html").body == r.body
+
+
+def test_swagger_document(hola_server):
+    srv = hola_server()
+    r = get(srv, "/api/swagger.json")
+    assert r.status == 200 and r.header("Content-Type") == "application/json"
+    assert r.header("Access-Control-Allow-Origin") == "*"
+    doc = json.loads(r.body)
+    assert doc["swagger"] == "2.0"
+    # SwaggerListener.java:31-40
+    assert doc["info"]["version"] == "1.0.0"
+    assert doc["info"]["title"] == "Hola microservices REST API"
+    assert doc["info"]["description"] == "Operations that can be invoked in the hola microservices"
+    assert doc["info"]["license"] == {"name": "Apache 2.0", "url": "http://www.apache.org/licenses/LICENSE-2.0.html"}
+    assert doc["info"]["contact"]["name"] == "developer@redhat.com"
+    assert doc["basePath"] == "/api" and doc["schemes"] == ["http"]
+    # @ApiOperation values, HolaResource.java:55,72,83
+    assert doc["paths"]["/hola"]["get"]["summary"] == "Returns the greeting in Spanish"
+    assert doc["paths"]["/hola-chaining"]["get"]["summary"] == "Returns the greeting plus the next service in the chain"
+    assert doc["paths"]["/health"]["get"]["summary"] == "Used to verify the health of the service"
+    assert doc["paths"]["/hola"]["get"]["produces"] == ["text/plain"]
+    assert doc["paths"]["/hola-chaining"]["get"]["produces"] == ["application/json"]
+    assert doc["paths"]["/hola-chaining"]["get"]["responses"]["200"]["schema"] == {"type": "array", "items": {"type": "string"}}
+    assert b'"swagger" : "2.0"' in r.body  # setPrettyPrint(true)
+    y = get(srv, "/api/swagger.yaml")
+    assert y.status == 200 and b'swagger: "2.0"' in y.body and b"/hola-chaining:" in y.body
+
+
+def test_webjars_directory(hola_server, tmp_path):
+    root = tmp_path / "webjars"
+    ui = root / "swagger-ui" / "2.1.4"
+    ui.mkdir(parents=True)
+    (ui / "index.html").write_text("<html>swagger ui</html>")
+    (ui / "swagger-ui.js").write_text("var x = 1;")
+    (tmp_path / "secret.txt").write_text("top secret")
+    srv = hola_server(args=["--webjars-dir", str(root)])
+    r = get(srv, "/webjars/swagger-ui/2.1.4/?url=http://x/api/swagger.json")
+    assert r.status == 200 and r.body == b"<html>swagger ui</html>" and r.header("Content-Type") == "text/html"
+    r = get(srv, "/webjars/swagger-ui/2.1.4/swagger-ui.js")
+    assert r.status == 200 and r.header("Content-Type") == "application/javascript"
+    assert get(srv, "/webjars/swagger-ui/2.1.4/missing.css").status == 404
+    assert get(srv, "/webjars/../secret.txt").status == 404
+    assert get(srv, "/webjars/%2e%2e/secret.txt").status == 404
+    assert get(srv, "/webjars/swagger-ui/2.1.4/..%2f..%2f..%2fsecret.txt").status == 404
+    # Without --webjars-dir the assets are simply absent (they are not on the build box either).
+    assert get(hola_server(), "/webjars/swagger-ui/2.1.4/index.html").status == 404
+
+
+def test_cli_version_help_and_bad_args(native_build):
+    import subprocess
+    exe = str(native_build.hola)
+    out = subprocess.run([exe, "--version"], capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.startswith("hola 0.0.1-SNAPSHOT")
+    out = subprocess.run([exe, "--help"], capture_output=True, text=True)
+    assert out.returncode == 0 and "-Dconf=FILE" in out.stdout
+    out = subprocess.run([exe, "--bogus"], capture_output=True, text=True)
+    assert out.returncode == 2 and "unknown argument" in out.stderr
+    out = subprocess.run([exe, "--port", "99999"], capture_output=True, text=True)
+    assert out.returncode == 2
+
+
+def test_port_in_use_is_reported(hola_server, native_build):
+    import subprocess
+    srv = hola_server(args=["--accept-mode", "rr"])  # no SO_REUSEPORT, so a second bind must fail
+    out = subprocess.run([str(native_build.hola), "--port", str(srv.port), "--bind", "127.0.0.1", "--accept-mode", "rr",
+                          "--threads", "1"], capture_output=True, text=True, timeout=10)
+    assert out.returncode == 1 and "bind" in out.stderr
+
+
+def test_swarm_style_port_definition(hola_server):
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    srv = hola_server(args=["-Dswarm.http.port=%d" % port])
+    assert srv.port == port
+    assert get(srv, "/api/health").status == 200

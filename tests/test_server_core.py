@@ -1,0 +1,171 @@
+"""HTTP/1.1 server behaviour that the reference inherits from Undertow and the rebuild has to
+supply itself: keep-alive, pipelining, partial reads, request bodies, limits, shutdown."""
+from __future__ import annotations
+
+import socket
+import threading
+import time
+
+import pytest
+
+from hola_b200 import client
+
+HOLA = b"Hola de unknown"
+
+
+def test_keep_alive_many_requests_one_connection(hola_server):
+    srv = hola_server()
+    with client.Connection("127.0.0.1", srv.port) as c:
+        for i in range(200):
+            r = c.request("GET", "/api/hola")
+            assert r.status == 200 and r.body == HOLA
+            assert r.header("Connection") == "keep-alive"
+
+
+def test_pipelined_requests_answered_in_order(hola_server):
+    srv = hola_server()
+    with client.Connection("127.0.0.1", srv.port) as c:
+        batch = b"".join(client.build_request("GET", t) for t in ("/api/hola", "/api/health", "/api/nothing", "/api/hola"))
+        c.send_raw(batch * 10)
+        for _ in range(10):
+            assert c.read_response().body == HOLA
+            assert c.read_response().body == b"I'm ok"
+            assert c.read_response().status == 404
+            assert c.read_response().body == HOLA
+
+
+def test_request_split_into_single_bytes(hola_server):
+    srv = hola_server()
+    with client.Connection("127.0.0.1", srv.port) as c:
+        for byte in client.build_request("GET", "/api/hola"):
+            c.send_raw(bytes([byte]))
+        assert c.read_response().body == HOLA
+        # ... and the connection is still usable afterwards.
+        assert c.request("GET", "/api/health").body == b"I'm ok"
+
+
+def test_connection_close_and_http10(hola_server):
+    srv = hola_server()
+    with client.Connection("127.0.0.1", srv.port) as c:
+        r = c.request("GET", "/api/hola", headers={"Connection": "close"})
+        assert r.status == 200 and r.header("Connection") == "close"
+        assert c.closed_by_peer()
+    with client.Connection("127.0.0.1", srv.port) as c:
+        r = c.request("GET", "/api/hola", version="HTTP/1.0")
+        assert r.status == 200 and r.body == HOLA and r.header("Connection") == "close"
+        assert c.closed_by_peer()
+    with client.Connection("127.0.0.1", srv.port) as c:
+        r = c.request("GET", "/api/hola", headers={"Connection": "keep-alive"}, version="HTTP/1.0")
+        assert r.header("Connection") == "keep-alive"
+        assert c.request("GET", "/api/health", headers={"Connection": "keep-alive"}, version="HTTP/1.0").body == b"I'm ok"
+
+
+def test_request_bodies_are_skipped_not_misparsed(hola_server):
+    srv = hola_server()
+    with client.Connection("127.0.0.1", srv.port) as c:
+        # A body that looks like a request must not be answered as one.
+        r = c.request("POST", "/api/hola", body=b"GET /api/health HTTP/1.1\r\nHost: x\r\n\r\n")
+        assert r.status == 405
+        assert c.request("GET", "/api/hola").body == HOLA
+        # Chunked body.
+        c.send_raw(b"POST /api/hola HTTP/1.1\r\nHost: x\r\nTransfer-Encoding: chunked\r\n\r\n"
+                   b"5\r\nhello\r\n1c\r\nGET /api/health HTTP/1.1\r\n\r\n\r\n0\r\n\r\n")
+        assert c.read_response().status == 405
+        assert c.request("GET", "/api/hola").body == HOLA
+        # Body arriving in pieces after the head.
+        c.send_raw(b"POST /api/health HTTP/1.1\r\nHost: x\r\nContent-Length: 10\r\n\r\n01234")
+        assert c.read_response().status == 405
+        c.send_raw(b"56789")
+        assert c.request("GET", "/api/health").body == b"I'm ok"
+
+
+def test_malformed_request_gets_400_and_close(hola_server):
+    srv = hola_server()
+    for raw in (b"NONSENSE\r\n\r\n", b"GET /api/hola HTTP/9.9\r\n\r\n", b"GET /api/hola HTTP/1.1\r\nBroken Header\r\n\r\n"):
+        with client.Connection("127.0.0.1", srv.port) as c:
+            c.send_raw(raw)
+            r = c.read_response()
+            assert r.status == 400 and r.header("Connection") == "close"
+            assert c.closed_by_peer()
+
+
+def test_oversized_head_gets_431(hola_server):
+    srv = hola_server(args=["--max-header-bytes", "4096"])
+    with client.Connection("127.0.0.1", srv.port) as c:
+        c.send_raw(b"GET /api/hola HTTP/1.1\r\nHost: x\r\nX-Filler: " + b"a" * 8000)
+        r = c.read_response()
+        assert r.status == 431
+        assert c.closed_by_peer()
+    # A large-but-allowed head still works (buffer growth path).
+    with client.Connection("127.0.0.1", srv.port) as c:
+        r = c.request("GET", "/api/hola", headers={"X-Filler": "b" * 3000})
+        assert r.status == 200
+
+
+def test_half_close_still_gets_the_answer(hola_server):
+    srv = hola_server()
+    with client.Connection("127.0.0.1", srv.port) as c:
+        c.send_raw(client.build_request("GET", "/api/hola"))
+        c.sock.shutdown(socket.SHUT_WR)
+        assert c.read_response().body == HOLA
+        assert c.closed_by_peer()
+
+
+def test_many_concurrent_connections(hola_server):
+    srv = hola_server(threads=4)
+    errors = []
+
+    def worker():
+        try:
+            with client.Connection("127.0.0.1", srv.port) as c:
+                for _ in range(50):
+                    if c.request("GET", "/api/hola").body != HOLA:
+                        errors.append("bad body")
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=worker) for _ in range(32)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors
+
+
+@pytest.mark.parametrize("mode", ["reuseport", "rr"])
+def test_accept_modes(hola_server, mode):
+    srv = hola_server(args=["--accept-mode", mode], threads=3)
+    conns = [client.Connection("127.0.0.1", srv.port) for _ in range(9)]
+    try:
+        for c in conns:
+            assert c.request("GET", "/api/hola").body == HOLA
+    finally:
+        for c in conns:
+            c.close()
+
+
+def test_idle_timeout(hola_server):
+    srv = hola_server(args=["--idle-timeout", "300"])
+    with client.Connection("127.0.0.1", srv.port) as c:
+        assert c.request("GET", "/api/hola").status == 200
+        assert c.closed_by_peer(timeout=3.0)
+
+
+def test_graceful_shutdown_finishes_in_flight_and_exits_zero(hola_server):
+    srv = hola_server()
+    with client.Connection("127.0.0.1", srv.port) as c:
+        assert c.request("GET", "/api/hola").status == 200
+        t0 = time.time()
+        code = srv.stop()
+        assert code == 0
+        assert time.time() - t0 < 3.0
+        assert c.closed_by_peer()
+
+
+def test_date_header_is_current_and_well_formed(hola_server):
+    import email.utils
+    srv = hola_server()
+    r = client.get("127.0.0.1", srv.port, "/api/hola")
+    parsed = email.utils.parsedate_to_datetime(r.header("Date"))
+    assert abs(parsed.timestamp() - time.time()) < 5
+    assert r.header("Date").endswith(" GMT") and len(r.header("Date")) == 29

@@ -1,0 +1,133 @@
+"""The C++ unit tests, the load generator and the bench/driver entry points."""
+from __future__ import annotations
+
+import json
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+from hola_b200 import client, loadgen
+
+REPO = Path(__file__).resolve().parent.parent
+
+
+def test_cpp_unit_tests_pass(native_build):
+    out = subprocess.run([str(native_build.unit_tests)], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "0 failed" in out.stdout
+
+
+def test_loadgen_closed_loop_counts_and_verifies(hola_server):
+    srv = hola_server()
+    rep = loadgen.run(srv.base_url + "/api/hola", connections=8, duration=1.0, warmup=0.5, interval=0.5, threads=2,
+                      expect_body=b"Hola de unknown")
+    assert rep["errors"]["total"] == 0 and rep["mode"] == "closed"
+    assert rep["requests"] > 100 and rep["rps"] > 100
+    assert len(rep["intervals"]) == 3 and rep["intervals"][0]["warmup"] is True and rep["intervals"][1]["warmup"] is False
+    assert rep["requests"] == sum(i["requests"] for i in rep["intervals"] if not i["warmup"])
+    lat = rep["latency_us"]
+    assert 0 < lat["min"] <= lat["p50"] <= lat["p99"] <= lat["max"]
+    # The server agrees on the order of magnitude of work done.
+    assert rep["bytes"] > rep["requests"] * 100
+
+
+def test_loadgen_detects_wrong_bodies_and_statuses(hola_server):
+    srv = hola_server()
+    rep = loadgen.run(srv.base_url + "/api/hola", connections=2, duration=0.3, warmup=0, interval=0.3, expect_body=b"something else",
+                      allow_errors=True)
+    assert rep["errors"]["body"] > 0 and rep["requests"] == 0
+    rep = loadgen.run(srv.base_url + "/api/missing", connections=2, duration=0.3, warmup=0, interval=0.3, allow_errors=True)
+    assert rep["errors"]["status"] > 0
+    with pytest.raises(RuntimeError, match="errors"):
+        loadgen.run(srv.base_url + "/api/missing", connections=1, duration=0.2, warmup=0, interval=0.2)
+    rep = loadgen.run(srv.base_url + "/api/missing", connections=2, duration=0.3, warmup=0, interval=0.3, expect_status=404)
+    assert rep["errors"]["total"] == 0 and rep["requests"] > 0
+
+
+def test_loadgen_open_loop_holds_the_rate(hola_server):
+    srv = hola_server()
+    rep = loadgen.run(srv.base_url + "/api/hola", connections=4, duration=2.0, warmup=0.5, interval=0.5, rate=2000, threads=2)
+    assert rep["mode"] == "open" and rep["errors"]["total"] == 0
+    assert 0.9 * 2000 <= rep["rps"] <= 1.1 * 2000, rep["rps"]
+
+
+def test_loadgen_pipelining_http10_and_connection_refused(hola_server):
+    srv = hola_server()
+    rep = loadgen.run(srv.base_url + "/api/hola", connections=2, duration=0.5, warmup=0, interval=0.5, pipeline=8,
+                      expect_body=b"Hola de unknown")
+    assert rep["errors"]["total"] == 0 and rep["requests"] > 100
+    rep = loadgen.run(srv.base_url + "/api/health", connections=2, duration=0.3, warmup=0, interval=0.3, http10=True,
+                      expect_body=b"I'm ok")
+    assert rep["errors"]["total"] == 0 and rep["reconnects"] == 0  # HTTP/1.0 keep-alive honoured
+    rep = loadgen.run("http://127.0.0.1:9/", connections=2, duration=0.3, warmup=0, interval=0.3, allow_errors=True)
+    assert rep["errors"]["connect"] > 0 and rep["requests"] == 0
+
+
+def test_loadgen_against_chunked_and_closing_servers(fake_aloha):
+    fake_aloha.mode = "chunked"
+    rep = loadgen.run(fake_aloha.url + "api/aloha-chaining", connections=2, duration=0.5, warmup=0, interval=0.5,
+                      expect_body=json.dumps(fake_aloha.payload).encode())
+    assert rep["errors"]["total"] == 0 and rep["requests"] > 5
+
+
+def _run_bench(*args, env=None, timeout=180):
+    e = dict(os.environ)
+    e.update(env or {})
+    out = subprocess.run([sys.executable, str(REPO / "bench.py"), *args], capture_output=True, text=True, timeout=timeout, env=e)
+    assert out.returncode == 0, out.stderr[-3000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1, out.stdout
+    return json.loads(lines[0])
+
+
+@pytest.mark.slow
+def test_bench_prints_one_contract_line():
+    r = _run_bench("--steps", "2", "--warmup", "3")
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "gpu_launches"):
+        assert key in r, key
+    assert r["n_gpus"] == 1 and r["steps"] == 2 and r["warmup"] == 3
+    assert r["value"] > 1000 and r["unit"] == "req/s" and r["higher_is_better"] is True
+    assert r["gpu_launches"] == 0  # stated, not hidden: there is no GPU work in this project
+    assert r["vs_baseline"] is None  # the reference publishes no number
+    assert r["e2e"]["h2d_bytes_per_step"] == 0 and r["e2e"]["value"] == r["value"]
+    assert r["config"]["connections_per_instance"] == 64
+    assert r["latency_us"]["p50"] <= r["latency_us"]["p99"]
+    assert "GET /api/hola" in r["metric"]
+
+
+def test_bench_reference_arm_reports_unavailable():
+    out = subprocess.run([sys.executable, str(REPO / "bench.py"), "--impl", "reference", "--gpus", "1", "--steps", "1", "--warmup", "1"],
+                         capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0
+    r = json.loads(out.stdout.strip().splitlines()[-1])
+    assert r["impl"] == "reference" and "unavailable" in r and len(r["unavailable"]) > 20
+
+
+@pytest.mark.slow
+def test_bench_two_instances_in_one_process():
+    r = _run_bench("--gpus", "2", "--steps", "1", "--warmup", "3")
+    assert r["n_gpus"] == 2 and r["config"]["global_batch"] == 128 and r["value"] > 1000
+
+
+@pytest.mark.slow
+def test_bench_under_torchrun_two_ranks():
+    e = dict(os.environ)
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                          "127.0.0.1", "--master-port", "29617", str(REPO / "bench.py"), "--gpus", "2", "--steps", "1", "--warmup", "3"],
+                         capture_output=True, text=True, timeout=300, env=e)
+    assert out.returncode == 0, out.stderr[-3000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    r = json.loads(lines[0])
+    assert r["n_gpus"] == 2 and r["requests"] > 1000
+
+
+def test_graft_entry_build_and_smoke():
+    sys.path.insert(0, str(REPO))
+    import __graft_entry__
+    __graft_entry__.build()
+    __graft_entry__.smoke()
