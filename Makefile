@@ -67,10 +67,13 @@ static: $(BUILD)/hola-static
 $(BUILD)/hola-static: $(BUILD)/obj/app/main.o $(BUILD)/libhola_core.a
 	$(CXX) -static -o $@ $^ $(LDFLAGS)
 
+# The sanitizer runtimes live next to the distribution compiler; a relocated toolchain named by
+# $CXX may not find them, so these variants prefer /usr/bin/g++ when it exists.
+SAN_CXX := $(firstword $(wildcard /usr/bin/g++) $(CXX))
 asan:
-	$(MAKE) VARIANT=asan
+	$(MAKE) VARIANT=asan CXX=$(SAN_CXX)
 tsan:
-	$(MAKE) VARIANT=tsan
+	$(MAKE) VARIANT=tsan CXX=$(SAN_CXX)
 
 test: $(BUILD)/hola_tests
 	$(BUILD)/hola_tests

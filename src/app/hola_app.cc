@@ -151,10 +151,17 @@ HolaApp::HolaApp(AppOptions options, GreetingService* greeting, Tracer* tracer, 
                             "\r\nAccept: */*\r\nConnection: keep-alive\r\nUser-Agent: hola-b200\r\n";
 }
 
-HolaApp::~HolaApp() = default;
+HolaApp::~HolaApp() {
+    // The workers (and their event loops) are gone by now; see Service::stop().
+    for (WorkerState* st : states_) delete st;
+}
 
 void HolaApp::on_worker_start(Worker& worker) {
     auto* st = new WorkerState();
+    {
+        std::lock_guard<std::mutex> lock(states_mu_);
+        states_.push_back(st);
+    }
     st->worker = &worker;
     if (tracer_->enabled()) st->ring = tracer_->register_producer();
     st->http.reset(new HttpClient(&worker.loop(), resolver_));
@@ -164,6 +171,15 @@ void HolaApp::on_worker_start(Worker& worker) {
 void HolaApp::on_worker_stop(Worker& worker) {
     WorkerState& st = state_of(worker);
     st.http->close_idle();
+}
+
+void HolaApp::on_worker_exit(Worker& worker) {
+    WorkerState& st = state_of(worker);
+    for (auto& kv : st.streams) {
+        if (kv.second.timer) worker.loop().cancel_timer(kv.second.timer);
+    }
+    st.streams.clear();
+    st.http.reset();  // unregisters its sockets from this worker's loop, which is still alive here
 }
 
 const GreetingSnapshot& HolaApp::current_greeting(WorkerState& st) {
@@ -193,6 +209,7 @@ void HolaApp::record_span(WorkerState& st, const TraceContext& ctx, bool client,
     size_t n = 0;
     for (std::string_view part : {url_a, url_b, url_c}) {
         const size_t take = std::min(part.size(), sizeof rec->url - n);
+        if (take == 0) continue;  // an empty view may carry a null pointer
         std::memcpy(rec->url + n, part.data(), take);
         n += take;
     }

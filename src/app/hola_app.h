@@ -16,8 +16,10 @@
 
 #include <atomic>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <unordered_map>
+#include <vector>
 
 #include "app/greeting.h"
 #include "app/tracer.h"
@@ -49,6 +51,7 @@ class HolaApp final : public Application {
 
     void on_worker_start(Worker& worker) override;
     void on_worker_stop(Worker& worker) override;
+    void on_worker_exit(Worker& worker) override;
     Disposition handle(Worker& worker, Connection& conn, const RequestHead& request) override;
     void on_connection_closed(Worker& worker, ConnRef ref) override;
 
@@ -87,6 +90,8 @@ class HolaApp final : public Application {
     Tracer* tracer_;
     Resolver* resolver_;
     HystrixCommand command_;
+    std::mutex states_mu_;
+    std::vector<WorkerState*> states_;  // one per worker thread, freed with the application
     std::atomic<int> stream_connections_{0};
     std::string aloha_request_prefix_;  // request line + fixed headers, B3 headers are appended
     std::string aloha_url_;             // for the client span's http.url tag

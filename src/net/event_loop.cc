@@ -130,8 +130,33 @@ void EventLoop::run() {
     constexpr int kMaxEvents = 256;
     epoll_event events[kMaxEvents];
     while (!stop_.load(std::memory_order_acquire)) {
-        const int n = epoll_wait(epfd_, events, kMaxEvents, next_timeout_ms());
+        const int timeout_ms = next_timeout_ms();
+        int n;
+        if (spin_ns_ > 0 && timeout_ms != 0) {
+            // Poll without sleeping while traffic is recent; fall back to a blocking wait after
+            // spin_ns_ of silence (or at the next timer, whichever is first).
+            n = epoll_wait(epfd_, events, kMaxEvents, 0);
+            while (n == 0) {
+                const int64_t t = monotonic_ns();
+                if (t - last_event_ns_ >= spin_ns_ || stop_.load(std::memory_order_relaxed)) break;
+                if (!timers_.empty() && timers_.top().deadline <= t) break;
+                __builtin_ia32_pause();
+                n = epoll_wait(epfd_, events, kMaxEvents, 0);
+            }
+            if (n == 0 && (timers_.empty() || timers_.top().deadline > monotonic_ns())) {
+                ++stats_.blocking_waits;
+                n = epoll_wait(epfd_, events, kMaxEvents, timeout_ms);
+            }
+        } else {
+            if (timeout_ms != 0) ++stats_.blocking_waits;
+            n = epoll_wait(epfd_, events, kMaxEvents, timeout_ms);
+        }
         refresh_clock();
+        ++stats_.iterations;
+        if (n > 0) {
+            stats_.events += static_cast<uint64_t>(n);
+            last_event_ns_ = now_ns_;
+        }
         if (n < 0) {
             if (errno == EINTR) continue;
             std::perror("hola: epoll_wait");

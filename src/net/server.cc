@@ -449,6 +449,7 @@ void Worker::thread_main() {
     loop_.refresh_clock();
     app_->on_worker_start(*this);
     if (listen_fd_ >= 0) loop_.add(listen_fd_, EPOLLIN, this);
+    loop_.set_spin_ns(static_cast<int64_t>(options_.spin_us) * 1000);
     if (options_.idle_timeout_ms > 0) {
         loop_.add_timer(loop_.now_ns() + static_cast<int64_t>(options_.idle_timeout_ms) * 500000,
                         [this] { sweep_idle(); });
@@ -461,6 +462,7 @@ void Worker::thread_main() {
             c->fd_ = -1;
         }
     }
+    app_->on_worker_exit(*this);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -527,6 +529,11 @@ ServerStats Server::stats() const {
         s.connections_open += w->stats_.connections_open.load(std::memory_order_relaxed);
         s.requests += w->stats_.requests.load(std::memory_order_relaxed);
         s.bad_requests += w->stats_.bad_requests.load(std::memory_order_relaxed);
+        if (!started_) {
+            s.loop_iterations += w->loop_.stats().iterations;
+            s.loop_events += w->loop_.stats().events;
+            s.loop_blocking_waits += w->loop_.stats().blocking_waits;
+        }
     }
     return s;
 }

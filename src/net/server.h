@@ -48,6 +48,9 @@ class Application {
     virtual void on_worker_start(Worker& /*worker*/) {}
     // Called once on each worker thread when it is shutting down.
     virtual void on_worker_stop(Worker& /*worker*/) {}
+    // Called on each worker thread after its event loop has returned for good; the place to
+    // destroy per-worker objects that are registered with that loop.
+    virtual void on_worker_exit(Worker& /*worker*/) {}
     virtual Disposition handle(Worker& worker, Connection& conn, const RequestHead& request) = 0;
     // A deferred or streaming connection was closed by the peer (or by shutdown).
     virtual void on_connection_closed(Worker& /*worker*/, ConnRef /*ref*/) {}
@@ -113,6 +116,7 @@ struct ServerOptions {
     std::vector<int> cpu_affinity;    // optional: worker i is pinned to cpu_affinity[i % size]
     int shutdown_grace_ms = 5000;
     int idle_timeout_ms = 0;          // 0: never close idle keep-alive connections
+    int spin_us = 0;                  // busy-poll window after the last event (EventLoop::set_spin_ns)
 };
 
 // Counters are kept per worker (single writer, so no cache line is shared between cores on
@@ -129,6 +133,10 @@ struct ServerStats {
     uint64_t connections_open = 0;
     uint64_t requests = 0;
     uint64_t bad_requests = 0;
+    // Event-loop counters, valid once the workers have stopped (they are plain, unsynchronised).
+    uint64_t loop_iterations = 0;
+    uint64_t loop_events = 0;
+    uint64_t loop_blocking_waits = 0;
 };
 
 class Worker final : public EventHandler {

@@ -65,6 +65,7 @@ struct Options {
     std::string expect_body;
     std::vector<std::string> headers;
     int timeout_ms = 5000;
+    int spin_us = 0;
     bool json = false;
     bool http10 = false;
 };
@@ -152,8 +153,27 @@ class LoadThread {
                 }
             }
             timespec ts{static_cast<time_t>(wait_ns / 1000000000), static_cast<long>(wait_ns % 1000000000)};
-            const int n = epoll_pwait2(epfd_, events, 256, &ts, nullptr);
+            int n = 0;
+            if (opt_.spin_us > 0) {
+                // Busy-poll while responses are expected; sleep only after spin_us of silence.
+                const int64_t spin_until = last_event_ns_ + static_cast<int64_t>(opt_.spin_us) * 1000;
+                const int64_t wait_until = now + wait_ns;
+                while ((n = epoll_wait(epfd_, events, 256, 0)) == 0) {
+                    const int64_t t = monotonic_ns();
+                    if (t >= spin_until || t >= wait_until) break;
+                    __builtin_ia32_pause();
+                }
+                if (n == 0) {
+                    const int64_t t = monotonic_ns();
+                    const int64_t left = wait_until > t ? wait_until - t : 0;
+                    timespec ts2{static_cast<time_t>(left / 1000000000), static_cast<long>(left % 1000000000)};
+                    n = epoll_pwait2(epfd_, events, 256, &ts2, nullptr);
+                }
+            } else {
+                n = epoll_pwait2(epfd_, events, 256, &ts, nullptr);
+            }
             if (n < 0 && errno != EINTR) break;
+            if (n > 0) last_event_ns_ = monotonic_ns();
             now = monotonic_ns();
             for (int i = 0; i < n; ++i) {
                 Conn& c = *static_cast<Conn*>(events[i].data.ptr);
@@ -446,6 +466,7 @@ class LoadThread {
     int64_t interval_ns_ = 0;
     int64_t end_ns_ = 0;
     int64_t last_sweep_ns_ = 0;
+    int64_t last_event_ns_ = 0;
     int epfd_ = -1;
     std::string request_;
     std::vector<Conn> conns_;
@@ -470,6 +491,7 @@ void usage() {
                  "  -H, --header 'K: V'    extra request header (repeatable)\n"
                  "      --http10           send HTTP/1.0 keep-alive requests\n"
                  "      --timeout-ms N     per-response timeout (5000)\n"
+                 "      --spin-us N        busy-poll for N us after the last event before sleeping (0)\n"
                  "      --json             machine-readable summary on stdout\n");
 }
 
@@ -563,6 +585,7 @@ int main(int argc, char** argv) {
         else if (a == "-H" || a == "--header") opt.headers.push_back(need(i));
         else if (a == "--http10") opt.http10 = true;
         else if (a == "--timeout-ms") opt.timeout_ms = std::atoi(need(i));
+        else if (a == "--spin-us") opt.spin_us = std::atoi(need(i));
         else if (a == "--json") opt.json = true;
         else if (a == "-h" || a == "--help") { usage(); return 0; }
         else if (!a.empty() && a[0] != '-') { if (!parse_url(a, &opt)) { std::fprintf(stderr, "hola-load: bad URL %s\n", a.c_str()); return 2; } }

@@ -35,6 +35,12 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "slow: takes more than a few seconds")
 
 
+def pytest_addoption(parser):
+    parser.addoption("--variant", default="release", choices=["release", "asan", "tsan"],
+                     help="which build of the hola executable the black-box tests launch "
+                          "(asan: AddressSanitizer+UBSan, tsan: ThreadSanitizer; SURVEY.md 5.2)")
+
+
 def pytest_sessionfinish(session, exitstatus):
     # `-m gpu` deselects everything by design; do not let that read as a failure.
     markexpr = getattr(session.config.option, "markexpr", "") or ""
@@ -52,20 +58,44 @@ def native_build():
 
 
 @pytest.fixture
-def hola_server():
-    """Factory: ``hola_server(args=[...], env={...}, threads=2)`` -> started HolaServer."""
+def hola_server(request):
+    """Factory: ``hola_server(args=[...], env={...}, threads=2)`` -> started HolaServer.
+
+    With ``--variant asan|tsan`` the sanitizer build is launched instead, and the teardown fails
+    the test if the sanitizer reported anything or the process did not exit cleanly.
+    """
+    variant = request.config.getoption("--variant")
+    if variant != "release":
+        hola_b200.build(variant)
     started: List[HolaServer] = []
 
     def start(args=(), env: Optional[Dict[str, Optional[str]]] = None, threads: int = 2, **kw) -> HolaServer:
         merged: Dict[str, Optional[str]] = {"HOSTNAME": None, "ZIPKIN_SERVER_URL": None, "hello": None}
+        if variant == "asan":
+            merged["ASAN_OPTIONS"] = "detect_leaks=1:abort_on_error=0:exitcode=66"
+            merged["UBSAN_OPTIONS"] = "print_stacktrace=1:halt_on_error=1:exitcode=66"
+        elif variant == "tsan":
+            merged["TSAN_OPTIONS"] = "halt_on_error=0:exitcode=66:second_deadlock_stack=1"
         merged.update(env or {})
-        srv = HolaServer(args=args, env=merged, threads=threads, **kw).start()
+        kw.setdefault("start_timeout", 10.0 if variant == "release" else 30.0)
+        srv = HolaServer(args=args, env=merged, threads=threads, variant=variant, **kw).start()
         started.append(srv)
         return srv
 
     yield start
+    problems = []
     for srv in started:
-        srv.stop()
+        code = srv.stop()
+        if variant != "release":
+            if code not in (0, None) or "Sanitizer" in srv.stderr or "runtime error:" in srv.stderr:
+                problems.append("exit %s\n%s" % (code, srv.stderr[-6000:]))
+    assert not problems, "sanitizer findings:\n" + "\n----\n".join(problems)
+
+
+class _FakeServer(ThreadingHTTPServer):
+    # The default accept backlog of 5 drops simultaneous connects when the machine is busy.
+    request_queue_size = 128
+    daemon_threads = True
 
 
 class _Recorder:
@@ -137,7 +167,7 @@ class FakeAloha(_Recorder):
                 self.end_headers()
                 self.wfile.write(body)
 
-        self.httpd = ThreadingHTTPServer(("127.0.0.1", 0), Handler)
+        self.httpd = _FakeServer(("127.0.0.1", 0), Handler)
         self.httpd.daemon_threads = True
         self.port = self.httpd.server_address[1]
         self.thread = threading.Thread(target=self.httpd.serve_forever, daemon=True)
@@ -174,7 +204,7 @@ class FakeZipkin(_Recorder):
                 self.send_header("Content-Length", "0")
                 self.end_headers()
 
-        self.httpd = ThreadingHTTPServer(("127.0.0.1", 0), Handler)
+        self.httpd = _FakeServer(("127.0.0.1", 0), Handler)
         self.httpd.daemon_threads = True
         self.port = self.httpd.server_address[1]
         self.thread = threading.Thread(target=self.httpd.serve_forever, daemon=True)
