@@ -34,7 +34,7 @@ LIB_OBJ  := $(patsubst src/%.cc,$(BUILD)/obj/%.o,$(LIB_SRC))
 TEST_SRC := $(wildcard tests/cpp/*.cc)
 TEST_OBJ := $(patsubst tests/cpp/%.cc,$(BUILD)/obj/tests/%.o,$(TEST_SRC))
 
-TARGETS := $(BUILD)/hola $(BUILD)/hola-load $(BUILD)/libhola.so $(BUILD)/hola_tests
+TARGETS := $(BUILD)/hola $(BUILD)/hola-load $(BUILD)/hola-coldstart $(BUILD)/libhola.so $(BUILD)/hola_tests
 
 .PHONY: all static asan tsan test clean
 all: $(TARGETS)
@@ -55,6 +55,9 @@ $(BUILD)/hola: $(BUILD)/obj/app/main.o $(BUILD)/libhola_core.a
 	$(CXX) -o $@ $^ $(LDFLAGS)
 
 $(BUILD)/hola-load: $(BUILD)/obj/tools/hola_load.o $(BUILD)/libhola_core.a
+	$(CXX) -o $@ $^ $(LDFLAGS)
+
+$(BUILD)/hola-coldstart: $(BUILD)/obj/tools/hola_coldstart.o $(BUILD)/libhola_core.a
 	$(CXX) -o $@ $^ $(LDFLAGS)
 
 $(BUILD)/libhola.so: $(BUILD)/obj/tools/capi.o $(BUILD)/libhola_core.a
@@ -81,4 +84,4 @@ test: $(BUILD)/hola_tests
 clean:
 	rm -rf build
 
--include $(LIB_OBJ:.o=.d) $(TEST_OBJ:.o=.d) $(BUILD)/obj/app/main.d $(BUILD)/obj/tools/hola_load.d $(BUILD)/obj/tools/capi.d
+-include $(LIB_OBJ:.o=.d) $(TEST_OBJ:.o=.d) $(BUILD)/obj/app/main.d $(BUILD)/obj/tools/hola_load.d $(BUILD)/obj/tools/hola_coldstart.d $(BUILD)/obj/tools/capi.d

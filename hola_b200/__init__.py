@@ -39,6 +39,10 @@ class Paths:
 
 
 def paths(variant: str = "release") -> Paths:
+    """Build outputs for a variant: release, asan, tsan, or static (the fully static executable
+    that goes into the FROM-scratch image; the other artefacts are the release ones)."""
+    if variant == "static":
+        return Paths(BUILD_DIR / "hola-static", BUILD_DIR / "hola-load", BUILD_DIR / "libhola.so", BUILD_DIR / "hola_tests")
     base = BUILD_DIR if variant == "release" else BUILD_DIR / variant
     return Paths(base / "hola", base / "hola-load", base / "libhola.so", base / "hola_tests")
 
@@ -60,7 +64,12 @@ def build(variant: str = "release", force: bool = False, quiet: bool = True) -> 
     if not force and p.all_exist() and not any(_sources_newer_than(t) for t in (p.hola, p.hola_load, p.libhola, p.unit_tests)):
         return p
     jobs = str(max(1, len(os.sched_getaffinity(0))))
-    cmd = ["make", "-C", str(REPO_ROOT), "-j", jobs, f"VARIANT={variant}"]
+    if variant == "static":
+        cmd = ["make", "-C", str(REPO_ROOT), "-j", jobs, "all", "static"]
+    elif variant == "release":
+        cmd = ["make", "-C", str(REPO_ROOT), "-j", jobs]
+    else:
+        cmd = ["make", "-C", str(REPO_ROOT), "-j", jobs, variant]  # asan / tsan pick their own compiler
     result = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if result.returncode != 0:
         raise RuntimeError("native build failed:\n" + result.stdout[-4000:])

@@ -8,6 +8,23 @@ from typing import Dict, Iterable, List, Optional, Sequence
 from . import build, paths
 
 
+def cold_start(command: Sequence[str], port: int, runs: int = 5, path: str = "/api/hola", timeout_ms: int = 30000,
+               env: Optional[Dict[str, str]] = None) -> Dict:
+    """Times exec() -> first HTTP 200 with ``build/hola-coldstart`` (BASELINE.json config 3).
+
+    ``command`` is the server's full command line; it must listen on ``port``.
+    """
+    exe = paths().hola_load.parent / "hola-coldstart"
+    if not exe.exists():
+        build(force=True)
+    cmd = [str(exe), "--port", str(port), "--path", path, "--runs", str(runs), "--timeout-ms", str(timeout_ms), "--", *command]
+    proc = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env,
+                          timeout=runs * (timeout_ms / 1000.0 + 5))
+    if proc.returncode != 0:
+        raise RuntimeError("hola-coldstart failed (%d): %s" % (proc.returncode, proc.stderr[-2000:]))
+    return json.loads(proc.stdout.strip().splitlines()[-1])
+
+
 def run(url: str, connections: int = 64, duration: float = 10.0, warmup: float = 1.0, interval: float = 1.0,
         threads: Optional[int] = None, cpus: Optional[Sequence[int]] = None, rate: Optional[float] = None,
         pipeline: int = 1, expect_status: int = 200, expect_body: Optional[bytes] = None,

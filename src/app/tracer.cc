@@ -2,7 +2,6 @@
 
 #include <arpa/inet.h>
 #include <fcntl.h>
-#include <netdb.h>
 #include <netinet/in.h>
 #include <netinet/tcp.h>
 #include <poll.h>
@@ -14,6 +13,7 @@
 #include <cstring>
 
 #include "core/http.h"
+#include "net/dns.h"
 
 namespace hola {
 
@@ -214,13 +214,9 @@ bool wait_fd(int fd, short events, int timeout_ms) {
 }
 
 int connect_with_timeout(const std::string& host, uint16_t port, int timeout_ms) {
-    addrinfo hints{};
-    hints.ai_family = AF_INET;
-    hints.ai_socktype = SOCK_STREAM;
-    addrinfo* res = nullptr;
-    if (getaddrinfo(host.c_str(), nullptr, &hints, &res) != 0 || !res) return -1;
-    sockaddr_in addr = *reinterpret_cast<sockaddr_in*>(res->ai_addr);
-    freeaddrinfo(res);
+    sockaddr_in addr{};
+    addr.sin_family = AF_INET;
+    if (resolve_ipv4(host, DnsConfig::load_system(), &addr.sin_addr.s_addr, timeout_ms) != DnsStatus::kOk) return -1;
     addr.sin_port = htons(port);
     const int fd = socket(AF_INET, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
     if (fd < 0) return -1;

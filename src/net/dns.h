@@ -1,0 +1,57 @@
+// A small stub resolver: /etc/hosts, then A-record queries to the name servers of
+// /etc/resolv.conf with search-list and ndots handling.
+//
+// Why not getaddrinfo(): the service is shipped as one fully static executable in a FROM-scratch
+// image (the analogue of the reference's self-contained uber-jar, /root/reference/pom.xml:230-241,
+// /root/reference/Dockerfile:10). A statically linked glibc still dlopen()s its NSS plug-ins at
+// run time, and in an empty image there are none - every lookup of the downstream service name
+// "aloha" (/root/reference/src/main/java/com/redhat/developers/msa/hola/HolaResource.java:95,103)
+// or of the Zipkin host (/root/reference/Dockerfile:6) would fail. In Kubernetes, "aloha" only
+// resolves through the search list in resolv.conf ("<ns>.svc.cluster.local ..."), so that logic
+// has to be here too.
+//
+// The lookup is blocking and meant for helper threads (net/resolver.h, app/tracer.cc); the event
+// loops never call it.
+#pragma once
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace hola {
+
+struct DnsConfig {
+    std::vector<std::string> nameservers;  // textual IPv4/IPv6 addresses
+    std::vector<std::string> search;
+    int ndots = 1;
+    int timeout_ms = 5000;  // per try (resolv.conf "options timeout:N", seconds)
+    int attempts = 2;
+    std::string hosts_file = "/etc/hosts";
+    uint16_t port = 53;     // overridable for tests (HOLA_DNS_PORT)
+
+    // Parses resolv.conf text. Missing name servers default to 127.0.0.1, as in libc.
+    static DnsConfig parse(const std::string& resolv_conf_text);
+    // Loads the system configuration. Environment overrides for tests and odd deployments:
+    // HOLA_RESOLV_CONF, HOLA_HOSTS_FILE, HOLA_DNS_PORT; LOCALDOMAIN replaces the search list.
+    static DnsConfig load_system();
+};
+
+enum class DnsStatus { kOk, kNotFound, kTimeout, kError };
+
+// Looks `host` up in the hosts file. Returns true and the address (network byte order).
+bool hosts_file_lookup(const std::string& path, const std::string& host, uint32_t* ipv4);
+
+// The candidate fully-qualified names for `host`, in the order a stub resolver tries them.
+std::vector<std::string> dns_candidates(const std::string& host, const DnsConfig& cfg);
+
+// Wire format helpers (exposed for unit tests).
+bool dns_build_query(const std::string& name, uint16_t id, std::vector<uint8_t>* out);
+// Parses a response to query `id` for `name`. kOk sets *ipv4 (network order) to the first A
+// record, following CNAMEs inside the message. *truncated is set when the TC bit is on.
+DnsStatus dns_parse_response(const uint8_t* data, size_t len, uint16_t id, uint32_t* ipv4, bool* truncated);
+
+// Full blocking lookup: literal, "localhost", hosts file, then DNS. `deadline_ms` bounds the
+// whole operation (0: only the per-try timeouts apply).
+DnsStatus resolve_ipv4(const std::string& host, const DnsConfig& cfg, uint32_t* ipv4, int deadline_ms = 0);
+
+}  // namespace hola

@@ -1,11 +1,12 @@
 #include "net/resolver.h"
 
 #include <arpa/inet.h>
-#include <netdb.h>
 #include <netinet/in.h>
 #include <sys/socket.h>
 
 #include <cstring>
+
+#include "net/dns.h"
 
 namespace hola {
 
@@ -77,16 +78,10 @@ void Resolver::thread_main(std::shared_ptr<State> st) {
             host = std::move(st->queue.front());
             st->queue.pop_front();
         }
-        addrinfo hints{};
-        hints.ai_family = AF_INET;
-        hints.ai_socktype = SOCK_STREAM;
-        addrinfo* res = nullptr;
+        // The system configuration is re-read per lookup (it is tiny, lookups are rare, and a
+        // pod's resolv.conf can be rewritten under a running process).
         Entry e;
-        if (getaddrinfo(host.c_str(), nullptr, &hints, &res) == 0 && res) {
-            e.ok = true;
-            e.ipv4 = reinterpret_cast<sockaddr_in*>(res->ai_addr)->sin_addr.s_addr;
-        }
-        if (res) freeaddrinfo(res);
+        e.ok = resolve_ipv4(host, DnsConfig::load_system(), &e.ipv4) == DnsStatus::kOk;
         e.expires_ns = monotonic_ns() + (e.ok ? st->positive_ttl_ns : st->negative_ttl_ns);
         // Answers are posted under the lock so that shutdown() (which takes it) cannot return
         // while a post to a soon-to-be-destroyed loop is still in progress.

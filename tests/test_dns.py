@@ -1,0 +1,167 @@
+"""The built-in stub resolver (src/net/dns.cc) against a fake DNS server: the downstream service is
+addressed by name ("aloha", HolaResource.java:95,103) and in Kubernetes that name only resolves
+through the pod's search list."""
+from __future__ import annotations
+
+import json
+import socket
+import struct
+import threading
+import time
+
+import pytest
+
+from hola_b200 import client
+
+FALLBACK = "Aloha response (fallback)"
+
+
+class FakeDns:
+    """Answers A queries from a dict; everything else is NXDOMAIN. Optionally slow or silent."""
+
+    def __init__(self, records):
+        self.records = {k.lower(): v for k, v in records.items()}
+        self.delay = 0.0
+        self.silent = False
+        self.queries = []
+        self.sock = socket.socket(socket.AF_INET, socket.SOCK_DGRAM)
+        self.sock.bind(("127.0.0.1", 0))
+        self.port = self.sock.getsockname()[1]
+        self.sock.settimeout(0.2)
+        self._stop = False
+        self.thread = threading.Thread(target=self._serve, daemon=True)
+        self.thread.start()
+
+    def _serve(self):
+        while not self._stop:
+            try:
+                data, addr = self.sock.recvfrom(2048)
+            except socket.timeout:
+                continue
+            except OSError:
+                return
+            qid = data[:2]
+            pos, labels = 12, []
+            while data[pos]:
+                n = data[pos]
+                labels.append(data[pos + 1:pos + 1 + n].decode())
+                pos += 1 + n
+            name = ".".join(labels).lower()
+            question = data[12:pos + 5]
+            self.queries.append(name)
+            if self.silent:
+                continue
+            if self.delay:
+                time.sleep(self.delay)
+            ip = self.records.get(name)
+            if ip is None:
+                reply = qid + b"\x81\x83" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
+            else:
+                answer = b"\xc0\x0c" + struct.pack(">HHIH", 1, 1, 30, 4) + socket.inet_aton(ip)
+                reply = qid + b"\x81\x80" + b"\x00\x01\x00\x01\x00\x00\x00\x00" + question + answer
+            self.sock.sendto(reply, addr)
+
+    def stop(self):
+        self._stop = True
+        self.thread.join(timeout=2)
+        self.sock.close()
+
+
+@pytest.fixture
+def fake_dns():
+    servers = []
+
+    def make(records):
+        d = FakeDns(records)
+        servers.append(d)
+        return d
+
+    yield make
+    for d in servers:
+        d.stop()
+
+
+def dns_env(tmp_path, dns, search="msa.svc.cluster.local svc.cluster.local", options="ndots:5 timeout:1 attempts:1"):
+    conf = tmp_path / "resolv.conf"
+    conf.write_text("nameserver 127.0.0.1\nsearch %s\noptions %s\n" % (search, options))
+    hosts = tmp_path / "hosts"
+    hosts.write_text("127.0.0.1 localhost\n")
+    return {"HOLA_RESOLV_CONF": str(conf), "HOLA_HOSTS_FILE": str(hosts), "HOLA_DNS_PORT": str(dns.port)}
+
+
+def chain(srv):
+    r = client.get("127.0.0.1", srv.port, "/api/hola-chaining")
+    assert r.status == 200
+    return json.loads(r.body)
+
+
+def test_service_name_resolves_through_the_search_list(hola_server, fake_aloha, fake_dns, tmp_path):
+    dns = fake_dns({"aloha.msa.svc.cluster.local": "127.0.0.1"})
+    srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port], env=dns_env(tmp_path, dns))
+    assert chain(srv) == ["Hola de unknown"] + fake_aloha.payload
+    assert dns.queries[0] == "aloha.msa.svc.cluster.local"
+    # Positive answers are cached (30 s, like the JVM): no second query.
+    n = len(dns.queries)
+    assert chain(srv)[1:] == fake_aloha.payload
+    assert len(dns.queries) == n
+    assert fake_aloha.snapshot()[0]["headers"]["host"] == "aloha:%d" % fake_aloha.port
+
+
+def test_second_search_domain_and_bare_name(hola_server, fake_aloha, fake_dns, tmp_path):
+    dns = fake_dns({"aloha.svc.cluster.local": "127.0.0.1"})
+    srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port], env=dns_env(tmp_path, dns))
+    assert chain(srv)[1:] == fake_aloha.payload
+    assert dns.queries[:2] == ["aloha.msa.svc.cluster.local", "aloha.svc.cluster.local"]
+    dns2 = fake_dns({"aloha": "127.0.0.1"})
+    srv2 = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port], env=dns_env(tmp_path, dns2))
+    assert chain(srv2)[1:] == fake_aloha.payload
+    assert dns2.queries == ["aloha.msa.svc.cluster.local", "aloha.svc.cluster.local", "aloha"]
+
+
+def test_unknown_name_falls_back_and_is_negatively_cached(hola_server, fake_dns, tmp_path):
+    dns = fake_dns({})
+    srv = hola_server(args=["-Dhystrix.command.default.circuitBreaker.enabled=false"], env=dns_env(tmp_path, dns))
+    assert chain(srv) == ["Hola de unknown", FALLBACK]
+    n = len(dns.queries)
+    assert n == 3
+    assert chain(srv) == ["Hola de unknown", FALLBACK]
+    assert len(dns.queries) == n  # 10 s negative cache, like the JVM
+
+
+def test_slow_dns_is_cut_off_by_the_command_timeout(hola_server, fake_aloha, fake_dns, tmp_path):
+    dns = fake_dns({"aloha.msa.svc.cluster.local": "127.0.0.1"})
+    dns.silent = True
+    env = dns_env(tmp_path, dns, options="ndots:5 timeout:5 attempts:2")
+    srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port], env=env)
+    t0 = time.time()
+    assert chain(srv) == ["Hola de unknown", FALLBACK]
+    assert 0.55 < time.time() - t0 < 1.2  # the 600 ms Hystrix timeout, not the resolver's 10 s
+    # Meanwhile the service keeps answering other requests.
+    assert client.get("127.0.0.1", srv.port, "/api/hola").status == 200
+    t0 = time.time()
+    assert srv.stop() == 0
+    assert time.time() - t0 < 3  # a lookup stuck on a dead name server does not hold up shutdown
+
+
+def test_hosts_file_beats_dns(hola_server, fake_aloha, fake_dns, tmp_path):
+    dns = fake_dns({})
+    env = dns_env(tmp_path, dns)
+    (tmp_path / "hosts").write_text("127.0.0.1 localhost\n127.0.0.1 aloha\n")
+    srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port], env=env)
+    assert chain(srv)[1:] == fake_aloha.payload
+    assert dns.queries == []
+
+
+def test_zipkin_host_is_resolved_the_same_way(hola_server, fake_zipkin, fake_dns, tmp_path):
+    dns = fake_dns({"zipkin-query.msa.svc.cluster.local": "127.0.0.1"})
+    env = dns_env(tmp_path, dns)
+    env["ZIPKIN_SERVER_URL"] = "http://zipkin-query:%d" % fake_zipkin.port  # Dockerfile:6 uses this host name
+    srv = hola_server(args=["--zipkin-flush-ms", "100"], env=env)
+    client.get("127.0.0.1", srv.port, "/api/hola")
+    assert len(fake_zipkin.wait_for_spans(1)) == 1
+    assert "zipkin-query.msa.svc.cluster.local" in dns.queries
+
+
+def test_resolve_flag_pins_a_name(hola_server, fake_aloha):
+    srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port, "--resolve", "aloha=127.0.0.1"])
+    assert chain(srv)[1:] == fake_aloha.payload
