@@ -227,6 +227,14 @@ bool Service::start(std::string* error) {
     if (started_) return true;
     const int64_t t_start = monotonic_ns();
 
+    // Every connection is a descriptor: use what the system allows rather than the usual soft
+    // default of 1024.
+    rlimit nofile{};
+    if (getrlimit(RLIMIT_NOFILE, &nofile) == 0 && nofile.rlim_cur < nofile.rlim_max) {
+        nofile.rlim_cur = nofile.rlim_max;
+        setrlimit(RLIMIT_NOFILE, &nofile);
+    }
+
     if (const char* h = std::getenv("HOSTNAME")) config_.app.hostname = h;
     std::string zipkin_url = config_.zipkin_url;
     if (!config_.zipkin_url_given) {

@@ -316,8 +316,17 @@ void Worker::on_events(uint32_t /*events*/) {
     while (listen_fd_ >= 0) {
         const int fd = accept4(listen_fd_, nullptr, nullptr, SOCK_NONBLOCK | SOCK_CLOEXEC);
         if (fd < 0) {
-            if (errno == EINTR) continue;
-            if (errno == EMFILE || errno == ENFILE) std::fprintf(stderr, "hola: accept: %s\n", std::strerror(errno));
+            if (errno == EINTR || errno == ECONNABORTED) continue;
+            if (errno == EMFILE || errno == ENFILE || errno == ENOBUFS || errno == ENOMEM) {
+                // Out of descriptors (or memory): the pending connection stays in the backlog and
+                // the listener stays readable, so a level-triggered loop would spin. Stop
+                // listening for a moment instead and let open connections finish.
+                std::fprintf(stderr, "hola: accept: %s - pausing accepts for 100 ms\n", std::strerror(errno));
+                loop_.remove(listen_fd_);
+                loop_.add_timer(loop_.now_ns() + 100000000, [this] {
+                    if (listen_fd_ >= 0 && !draining_) loop_.add(listen_fd_, EPOLLIN, this);
+                });
+            }
             return;
         }
         set_nodelay(fd);

@@ -169,3 +169,51 @@ def test_date_header_is_current_and_well_formed(hola_server):
     parsed = email.utils.parsedate_to_datetime(r.header("Date"))
     assert abs(parsed.timestamp() - time.time()) < 5
     assert r.header("Date").endswith(" GMT") and len(r.header("Date")) == 29
+
+
+def test_descriptor_exhaustion_does_not_spin_or_die(hola_server, native_build):
+    """With the fd limit reached, new connections wait in the backlog; the ones already open keep
+    being served, the process does not burn a core on accept(), and service resumes afterwards."""
+    import resource
+    import subprocess
+    import os
+
+    # Launch with a tiny hard limit so the service cannot raise it.
+    def limit():
+        resource.setrlimit(resource.RLIMIT_NOFILE, (40, 40))
+
+    env = {k: v for k, v in os.environ.items() if k not in ("HOSTNAME", "ZIPKIN_SERVER_URL")}
+    proc = subprocess.Popen([str(native_build.hola), "--port", "0", "--bind", "127.0.0.1", "--threads", "1"],
+                            stderr=subprocess.PIPE, text=True, env=env, preexec_fn=limit)
+    try:
+        line = proc.stderr.readline()
+        port = int(line.split("127.0.0.1:")[1].split()[0])
+        conns = []
+        for _ in range(60):  # more than the limit allows
+            try:
+                c = client.Connection("127.0.0.1", port, timeout=1.0)
+                conns.append(c)
+            except OSError:
+                break
+        # The earliest connections still work.
+        assert conns[0].request("GET", "/api/hola").body == HOLA
+        assert conns[5].request("GET", "/api/health").body == b"I'm ok"
+        t0 = time.process_time()
+        ru0 = resource.getrusage(resource.RUSAGE_CHILDREN)
+        time.sleep(0.5)
+        # Free descriptors; the backlog drains and late connections get answered.
+        for c in conns[:30]:
+            c.close()
+        time.sleep(0.3)
+        late = conns[-1]
+        late.sock.settimeout(3.0)
+        assert late.request("GET", "/api/hola").body == HOLA
+        for c in conns[30:]:
+            c.close()
+    finally:
+        proc.terminate()
+        out = proc.communicate(timeout=10)[1]
+    assert proc.returncode == 0
+    assert "pausing accepts" in out
+    ru = resource.getrusage(resource.RUSAGE_CHILDREN)
+    assert (ru.ru_utime + ru.ru_stime) < 0.5  # a spinning accept loop would have burnt ~1 s of CPU

@@ -126,6 +126,23 @@ def test_bench_under_torchrun_two_ranks():
     assert r["n_gpus"] == 2 and r["requests"] > 1000
 
 
+def test_differential_tool_same_and_different(hola_server):
+    """tools/differential.py: the harness kept ready for a runnable Java reference."""
+    a = hola_server()
+    b = hola_server(args=["--accept-mode", "rr"], threads=1)
+    c = hola_server(args=["-Dhello=Bonjour de %s"])
+    tool = str(REPO / "tools" / "differential.py")
+    same = subprocess.run([sys.executable, tool, a.base_url, b.base_url, "--json"], capture_output=True, text=True, timeout=120)
+    assert same.returncode == 0, same.stdout[-2000:] + same.stderr[-2000:]
+    rep = json.loads(same.stdout)
+    assert rep["requests"] >= 20 and rep["contract_differences"] == 0
+    diff = subprocess.run([sys.executable, tool, a.base_url, c.base_url, "--json"], capture_output=True, text=True, timeout=120)
+    assert diff.returncode == 1
+    rep = json.loads(diff.stdout)
+    changed = [r["request"] for r in rep["report"] if r["contract"]]
+    assert any("/api/hola" in r for r in changed) and not any("/api/health" in r for r in changed)
+
+
 def test_graft_entry_build_and_smoke():
     sys.path.insert(0, str(REPO))
     import __graft_entry__
