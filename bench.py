@@ -219,6 +219,8 @@ def main() -> int:
             "global_batch": CONNECTIONS * n,
             "seq_len": None,
             "parallelism": "%d independent instance(s), one per rank" % n,
+            "scaling_note": "instances share this machine's %d CPUs (each gets a disjoint slice, half server / half load "
+                            "generator), so the aggregate is bounded by the same cores at every N; GPUs are not involved" % len(cpus),
             "connections_per_instance": CONNECTIONS,
             "mode": args.mode,
             "server_cpus": first["server_cpus"],

@@ -35,6 +35,17 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "slow: takes more than a few seconds")
 
 
+def pytest_report_header(config):
+    """Build the native artefacts and load libhola.so before anything is collected.
+
+    Every test exercises native code (the executable or the library); if it cannot be built or
+    loaded the session should say so at the top instead of failing test by test.
+    """
+    from hola_b200 import native
+    hola_b200.build()
+    return "hola native library: %s (version %s)" % (hola_b200.paths().libhola, native.version())
+
+
 def pytest_addoption(parser):
     parser.addoption("--variant", default="release", choices=["release", "asan", "tsan", "static"],
                      help="which build of the hola executable the black-box tests launch "
