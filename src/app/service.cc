@@ -1,5 +1,7 @@
 #include "app/service.h"
 
+#include "core/text.h"
+
 #include <arpa/inet.h>
 #include <sys/resource.h>
 
@@ -47,32 +49,6 @@ std::string usage_text() {
 }
 
 namespace {
-
-bool parse_cpu_list(const std::string& s, std::vector<int>* out) {
-    size_t i = 0;
-    while (i < s.size()) {
-        size_t comma = s.find(',', i);
-        if (comma == std::string::npos) comma = s.size();
-        const std::string part = s.substr(i, comma - i);
-        i = comma + 1;
-        if (part.empty()) continue;
-        const size_t dash = part.find('-');
-        char* end = nullptr;
-        if (dash == std::string::npos) {
-            const long v = std::strtol(part.c_str(), &end, 10);
-            if (*end != '\0' || v < 0) return false;
-            out->push_back(static_cast<int>(v));
-        } else {
-            const std::string lo = part.substr(0, dash), hi = part.substr(dash + 1);
-            const long a = std::strtol(lo.c_str(), &end, 10);
-            if (lo.empty() || *end != '\0' || a < 0) return false;
-            const long b = std::strtol(hi.c_str(), &end, 10);
-            if (hi.empty() || *end != '\0' || b < a) return false;
-            for (long v = a; v <= b; ++v) out->push_back(static_cast<int>(v));
-        }
-    }
-    return !out->empty();
-}
 
 bool parse_uint(const std::string& s, long max, long* out) {
     if (s.empty() || s.size() > 10) return false;

@@ -128,6 +128,37 @@ std::string to_upper_java(std::string_view s) {
     return out;
 }
 
+bool parse_cpu_list(std::string_view text, std::vector<int>* out) {
+    auto number = [](std::string_view s, int* v) {
+        if (s.empty() || s.size() > 6) return false;
+        int n = 0;
+        for (char c : s) {
+            if (c < '0' || c > '9') return false;
+            n = n * 10 + (c - '0');
+        }
+        *v = n;
+        return true;
+    };
+    size_t i = 0;
+    while (i <= text.size()) {
+        size_t comma = text.find(',', i);
+        if (comma == std::string_view::npos) comma = text.size();
+        const std::string_view part = text.substr(i, comma - i);
+        i = comma + 1;
+        if (part.empty()) continue;
+        const size_t dash = part.find('-');
+        int a = 0, b = 0;
+        if (dash == std::string_view::npos) {
+            if (!number(part, &a)) return false;
+            out->push_back(a);
+        } else {
+            if (!number(part.substr(0, dash), &a) || !number(part.substr(dash + 1), &b) || b < a) return false;
+            for (int v = a; v <= b; ++v) out->push_back(v);
+        }
+    }
+    return !out->empty();
+}
+
 void Utf16Assembler::push_unit(uint16_t unit) {
     if (pending_high_ != 0) {
         if (unit >= 0xDC00 && unit <= 0xDFFF) {

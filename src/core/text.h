@@ -9,6 +9,7 @@
 #include <cstdint>
 #include <string>
 #include <string_view>
+#include <vector>
 
 namespace hola {
 
@@ -46,6 +47,9 @@ class Utf16Assembler {
     std::string* out_;
     uint16_t pending_high_ = 0;
 };
+
+// Parses a CPU list such as "0,2,4-7" into {0,2,4,5,6,7}. Returns false on anything else.
+bool parse_cpu_list(std::string_view text, std::vector<int>* out);
 
 inline bool is_hex_digit(char c) {
     return (c >= '0' && c <= '9') || (c >= 'a' && c <= 'f') || (c >= 'A' && c <= 'F');

@@ -42,6 +42,7 @@
 
 #include "core/histogram.h"
 #include "core/http.h"
+#include "core/text.h"
 #include "net/event_loop.h"  // monotonic_ns
 
 using namespace hola;
@@ -495,26 +496,6 @@ void usage() {
                  "      --json             machine-readable summary on stdout\n");
 }
 
-bool parse_cpus(const std::string& s, std::vector<int>* out) {
-    size_t i = 0;
-    while (i < s.size()) {
-        size_t comma = s.find(',', i);
-        if (comma == std::string::npos) comma = s.size();
-        const std::string part = s.substr(i, comma - i);
-        i = comma + 1;
-        if (part.empty()) continue;
-        const size_t dash = part.find('-');
-        if (dash == std::string::npos) {
-            out->push_back(std::atoi(part.c_str()));
-        } else {
-            const int a = std::atoi(part.substr(0, dash).c_str());
-            const int b = std::atoi(part.substr(dash + 1).c_str());
-            for (int v = a; v <= b; ++v) out->push_back(v);
-        }
-    }
-    return !out->empty();
-}
-
 bool parse_url(const std::string& url, Options* o) {
     static const std::string kScheme = "http://";
     if (url.compare(0, kScheme.size(), kScheme) != 0) return false;
@@ -569,7 +550,9 @@ int main(int argc, char** argv) {
         else if (a == "-w" || a == "--warmup") opt.warmup_s = std::atof(need(i));
         else if (a == "-i" || a == "--interval") opt.interval_s = std::atof(need(i));
         else if (a == "-t" || a == "--threads") opt.threads = std::atoi(need(i));
-        else if (a == "--cpus") parse_cpus(need(i), &opt.cpus);
+        else if (a == "--cpus") {
+            if (!parse_cpu_list(need(i), &opt.cpus)) { std::fprintf(stderr, "hola-load: bad --cpus list\n"); return 2; }
+        }
         else if (a == "--rate") opt.rate = std::atof(need(i));
         else if (a == "--pipeline") opt.pipeline = std::atoi(need(i));
         else if (a == "--expect-status") opt.expect_status = std::atoi(need(i));
