@@ -133,7 +133,9 @@ struct HolaApp::ChainCall {
     int64_t client_start_us = 0;
     int64_t exec_start_ns = 0;
     HttpClient::RequestId request = 0;
-    EventLoop::TimerId timer = 0;
+    EventLoop::TimerId timer = 0;        // the command timeout
+    EventLoop::TimerId retry_timer = 0;  // pause before the next attempt
+    int attempt = 0;
 };
 
 HolaApp::HolaApp(AppOptions options, GreetingService* greeting, Tracer* tracer, Resolver* resolver)
@@ -409,7 +411,39 @@ void HolaApp::start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& cal
         finish_chain(st, call, JsonStringList{options_.fallback});
         return;
     }
-    call->client_ctx = start_client_trace(call->server_ctx, &st.ids);
+    call->exec_start_ns = loop.now_ns();
+
+    WorkerState* stp = &st;
+    if (options_.breaker.timeout_enabled) {
+        call->timer = loop.add_timer(
+            loop.now_ns() + static_cast<int64_t>(options_.breaker.timeout_ms) * 1000000, [this, stp, call] {
+                if (call->settled) return;
+                call->settled = true;
+                call->timer = 0;
+                EventLoop& lp = stp->worker->loop();
+                if (call->retry_timer) {
+                    lp.cancel_timer(call->retry_timer);
+                    call->retry_timer = 0;
+                }
+                stp->http->cancel(call->request);
+                command_.complete_timeout(lp.now_ns() / 1000000,
+                                          static_cast<int>((lp.now_ns() - call->exec_start_ns) / 1000000));
+                if (options_.verbose) std::fprintf(stderr, "hola: aloha call timed out -> fallback\n");
+                finish_chain(*stp, call, JsonStringList{options_.fallback});
+            });
+    }
+    send_chain_attempt(st, call);
+}
+
+// One HTTP attempt of the downstream call. Connection-level failures are retried the way Feign's
+// default Retryer does (the reference builds its client with HystrixFeign.builder() and does not
+// replace the retryer, HolaResource.java:104-112): up to feign_max_attempts tries, sleeping
+// 100 ms x 1.5^k (capped at 1 s) between them - all inside the one Hystrix command, so the
+// 600 ms command timeout is what usually ends a series of failing attempts. HTTP error statuses
+// and undecodable bodies are not retried.
+void HolaApp::send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCall>& call) {
+    ++call->attempt;
+    call->client_ctx = start_client_trace(call->server_ctx, &st.ids);  // a fresh client span per attempt
     std::string request = aloha_request_prefix_;
     if (st.ring) {
         if (call->client_ctx.sampled) {
@@ -422,36 +456,36 @@ void HolaApp::start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& cal
         }
     }
     request.append("\r\n");
-    call->exec_start_ns = loop.now_ns();
     call->client_start_us = realtime_us();
-
     WorkerState* stp = &st;
-    if (options_.breaker.timeout_enabled) {
-        call->timer = loop.add_timer(
-            loop.now_ns() + static_cast<int64_t>(options_.breaker.timeout_ms) * 1000000, [this, stp, call] {
-                if (call->settled) return;
-                call->settled = true;
-                call->timer = 0;
-                stp->http->cancel(call->request);
-                EventLoop& lp = stp->worker->loop();
-                command_.complete_timeout(lp.now_ns() / 1000000,
-                                          static_cast<int>((lp.now_ns() - call->exec_start_ns) / 1000000));
-                if (options_.verbose) std::fprintf(stderr, "hola: aloha call timed out -> fallback\n");
-                finish_chain(*stp, call, JsonStringList{options_.fallback});
-            });
-    }
     if (options_.verbose) std::fprintf(stderr, "[AlohaService#aloha] ---> GET %s HTTP/1.1\n", aloha_url_.c_str());
     call->request = st.http->send(
         options_.aloha_host, options_.aloha_port, std::move(request), [this, stp, call](ClientResult&& r) {
             if (call->settled) return;
-            call->settled = true;
             EventLoop& lp = stp->worker->loop();
+            const int64_t now_ns = monotonic_ns();
+            const int exec_ms = static_cast<int>((now_ns - call->exec_start_ns) / 1000000);
+            const bool io_failure = r.code == ClientResult::Code::kResolveFailed || r.code == ClientResult::Code::kConnectFailed ||
+                                    r.code == ClientResult::Code::kIoError;
+            if (io_failure && call->attempt < options_.feign_max_attempts) {
+                double interval_ms = options_.feign_retry_period_ms;
+                for (int k = 0; k < call->attempt; ++k) interval_ms *= 1.5;
+                if (interval_ms > options_.feign_retry_max_period_ms) interval_ms = options_.feign_retry_max_period_ms;
+                if (options_.verbose) {
+                    std::fprintf(stderr, "[AlohaService#aloha] <--- ERROR %s (%dms)\n[AlohaService#aloha] ---> RETRYING in %.0f ms\n",
+                                 r.describe(), exec_ms, interval_ms);
+                }
+                call->retry_timer = lp.add_timer(now_ns + static_cast<int64_t>(interval_ms * 1e6), [this, stp, call] {
+                    call->retry_timer = 0;
+                    if (!call->settled) send_chain_attempt(*stp, call);
+                });
+                return;
+            }
+            call->settled = true;
             if (call->timer) {
                 lp.cancel_timer(call->timer);
                 call->timer = 0;
             }
-            const int64_t now_ns = monotonic_ns();
-            const int exec_ms = static_cast<int>((now_ns - call->exec_start_ns) / 1000000);
             JsonStringList tail;
             bool ok = false;
             std::string why;

@@ -39,6 +39,10 @@ struct AppOptions {
     std::string fallback = "Aloha response (fallback)";  // HolaResource.java:112
     std::string webjars_dir;                      // empty: /webjars/** answers 404
     BreakerConfig breaker = BreakerConfig::reference_defaults();
+    // Feign's default Retryer (period 100 ms, max period 1 s, 5 attempts); 1 attempt = no retry.
+    int feign_max_attempts = 5;
+    int feign_retry_period_ms = 100;
+    int feign_retry_max_period_ms = 1000;
     int stream_max_connections = 5;               // hystrix.stream.maxConcurrentConnections default
     int stream_default_delay_ms = 500;
     bool verbose = false;
@@ -76,6 +80,7 @@ class HolaApp final : public Application {
 
     // Downstream call with breaker, timeout and fallback.
     void start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call);
+    void send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCall>& call);
     void finish_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call, JsonStringList&& tail);
 
     // Tracing.

@@ -32,6 +32,8 @@ std::string usage_text() {
            "  --cpus LIST                 pin thread i to the i-th CPU of LIST (e.g. 0,1,2,3 or 0-3)\n"
            "  --accept-mode MODE          reuseport (default; one listener per thread) | rr (one acceptor, round-robin)\n"
            "  --aloha-url URL             downstream base URL (default http://aloha:8080/)\n"
+           "  --feign-max-attempts N      tries per downstream call on connection failures (default 5, as Feign's\n"
+           "                              default Retryer: pauses of 150, 225, 337, 506 ms; 1 disables retrying)\n"
            "  --resolve NAME=IPV4         answer lookups of NAME with IPV4 instead of asking the system resolver\n"
            "  --zipkin-url URL            overrides env ZIPKIN_SERVER_URL; unset/empty disables tracing\n"
            "  --zipkin-flush-ms N         span reporter period (default 1000)\n"
@@ -111,6 +113,9 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
             cfg->app.aloha_host = host;
             cfg->app.aloha_port = port;
             cfg->app.aloha_path = path + "/api/aloha-chaining";
+        } else if (a == "--feign-max-attempts") {
+            if (!value(&v) || !parse_uint(v, 100, &n) || n == 0) return fail("--feign-max-attempts needs a number >= 1");
+            cfg->app.feign_max_attempts = static_cast<int>(n);
         } else if (a == "--resolve") {
             if (!value(&v)) return fail("--resolve needs NAME=IPV4");
             const size_t eq = v.find('=');

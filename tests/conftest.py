@@ -131,6 +131,7 @@ class FakeAloha(_Recorder):
         self.mode = "ok"
         self.payload = ["Aloha mai fake-aloha", "Olá de fake-ola", "Bonjour de fake-bonjour"]
         self.delay = 0.0
+        self.fail_first = 0  # drop this many upcoming requests without answering
         fake = self
 
         class Handler(BaseHTTPRequestHandler):
@@ -144,6 +145,10 @@ class FakeAloha(_Recorder):
                 if fake.delay:
                     time.sleep(fake.delay)
                 mode = fake.mode
+                with fake.lock:
+                    if fake.fail_first > 0:
+                        fake.fail_first -= 1
+                        mode = "close"
                 if mode == "ok":
                     body = json.dumps(fake.payload).encode()
                     self._reply(200, body, "application/json")

@@ -47,12 +47,42 @@ def test_chaining_downstream_chunked_and_keepalive_reuse(hola_server, fake_aloha
 
 
 def test_fallback_when_downstream_unreachable(hola_server):
-    # Nothing listens on the discard port.
+    """Nothing listens on the discard port. Feign's default Retryer keeps trying (pauses of 150,
+    225, 337 ms ...) inside the Hystrix command, so it is the 600 ms command timeout that ends
+    the call - the fallback arrives after ~600 ms, not immediately."""
     srv = hola_server(args=["--aloha-url", "http://127.0.0.1:9/"])
     t0 = time.time()
     r = chain(srv)
     assert json.loads(r.body) == ["Hola de unknown", FALLBACK]  # HolaResource.java:112
-    assert time.time() - t0 < 0.5  # a refused connection fails fast, no need to wait for the timeout
+    assert 0.55 <= time.time() - t0 < 1.2
+    # With retrying switched off a refused connection fails fast.
+    srv2 = hola_server(args=["--aloha-url", "http://127.0.0.1:9/", "--feign-max-attempts", "1"])
+    t0 = time.time()
+    assert json.loads(chain(srv2).body) == ["Hola de unknown", FALLBACK]
+    assert time.time() - t0 < 0.3
+
+
+def test_connection_failures_are_retried_like_feign(hola_server, fake_aloha):
+    """First attempt: the downstream drops the connection without answering (an IOException to
+    Feign). The default Retryer waits 150 ms and tries again; the second attempt succeeds and
+    the caller never sees the hiccup."""
+    fake_aloha.fail_first = 1
+    srv = hola_server(args=["--aloha-url", fake_aloha.url])
+    t0 = time.time()
+    assert json.loads(chain(srv).body) == ["Hola de unknown"] + fake_aloha.payload
+    elapsed = time.time() - t0
+    assert 0.14 <= elapsed < 0.5, elapsed
+    assert len(fake_aloha.snapshot()) == 2
+    # Two failures: 150 + 225 ms of pauses, still inside the 600 ms budget.
+    fake_aloha.fail_first = 2
+    t0 = time.time()
+    assert json.loads(chain(srv).body) == ["Hola de unknown"] + fake_aloha.payload
+    assert 0.37 <= time.time() - t0 < 0.6
+    # HTTP error statuses are not retried.
+    fake_aloha.mode = "500"
+    before = len(fake_aloha.snapshot())
+    assert json.loads(chain(srv).body) == ["Hola de unknown", FALLBACK]
+    assert len(fake_aloha.snapshot()) == before + 1
 
 
 def test_fallback_when_name_does_not_resolve(hola_server):

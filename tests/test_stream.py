@@ -93,7 +93,7 @@ def test_stream_reports_command_and_pool_after_calls(hola_server, fake_aloha):
 
 
 def test_stream_shows_open_circuit(hola_server):
-    srv = hola_server(args=["--aloha-url", "http://127.0.0.1:9/"], threads=1)
+    srv = hola_server(args=["--aloha-url", "http://127.0.0.1:9/", "--feign-max-attempts", "1"], threads=1)
     for _ in range(6):
         client.get("127.0.0.1", srv.port, "/api/hola-chaining")
     time.sleep(0.6)
