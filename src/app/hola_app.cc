@@ -136,6 +136,7 @@ struct HolaApp::ChainCall {
     EventLoop::TimerId timer = 0;        // the command timeout
     EventLoop::TimerId retry_timer = 0;  // pause before the next attempt
     int attempt = 0;
+    bool failed_without_fallback = false;
 };
 
 HolaApp::HolaApp(AppOptions options, GreetingService* greeting, Tracer* tracer, Resolver* resolver)
@@ -224,7 +225,8 @@ Disposition HolaApp::handle(Worker& worker, Connection& conn, const RequestHead&
     const std::string_view path = rq.path;
     std::string& out = conn.out();
 
-    if (path.size() >= 5 && std::memcmp(path.data(), "/api/", 5) == 0) {
+    // The JAX-RS servlet is mapped to /api/* (JaxRsActivator.java:30), which also covers "/api".
+    if ((path.size() >= 5 && std::memcmp(path.data(), "/api/", 5) == 0) || path == "/api") {
         const ApiRoute route = match_api(path.substr(4));
         if (route == ApiRoute::kNone) {
             std::string body = "RESTEASY003210: Could not find resource for full path: http://";
@@ -398,6 +400,14 @@ Disposition HolaApp::serve_chaining(WorkerState& st, Connection& conn, const Req
     return Disposition::kDeferred;
 }
 
+// What a failed, timed-out, rejected or short-circuited call contributes to the response: the
+// static fallback list (HolaResource.java:112), or nothing when fallbacks are disabled.
+JsonStringList HolaApp::fallback_tail(ChainCall& call) const {
+    if (options_.breaker.fallback_enabled) return JsonStringList{options_.fallback};
+    call.failed_without_fallback = true;
+    return {};
+}
+
 void HolaApp::start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call) {
     EventLoop& loop = st.worker->loop();
     const int64_t now_ms = loop.now_ns() / 1000000;
@@ -408,7 +418,7 @@ void HolaApp::start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& cal
                          adm == HystrixCommand::Admission::kShortCircuited ? "short-circuited" : "rejected (pool full)");
         }
         call->settled = true;
-        finish_chain(st, call, JsonStringList{options_.fallback});
+        finish_chain(st, call, fallback_tail(*call));
         return;
     }
     call->exec_start_ns = loop.now_ns();
@@ -429,7 +439,7 @@ void HolaApp::start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& cal
                 command_.complete_timeout(lp.now_ns() / 1000000,
                                           static_cast<int>((lp.now_ns() - call->exec_start_ns) / 1000000));
                 if (options_.verbose) std::fprintf(stderr, "hola: aloha call timed out -> fallback\n");
-                finish_chain(*stp, call, JsonStringList{options_.fallback});
+                finish_chain(*stp, call, fallback_tail(*call));
             });
     }
     send_chain_attempt(st, call);
@@ -513,7 +523,7 @@ void HolaApp::send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCal
                 finish_chain(*stp, call, std::move(tail));
             } else {
                 command_.complete_failure(now_ns / 1000000, exec_ms);
-                finish_chain(*stp, call, JsonStringList{options_.fallback});
+                finish_chain(*stp, call, fallback_tail(*call));
             }
         });
 }
@@ -521,16 +531,24 @@ void HolaApp::send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCal
 void HolaApp::finish_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call, JsonStringList&& tail) {
     if (call->finished) return;
     call->finished = true;
-    JsonStringList all;
-    all.reserve(tail.size() + 1);
-    all.emplace_back(std::move(call->hola_text));
-    for (auto& item : tail) all.emplace_back(std::move(item));
-    const std::string body = json_encode_string_list(all);
     Worker& worker = *st.worker;
     const bool close = call->close || worker.draining();
     std::string response;
-    append_response(&response, 200, kJson, body, true, close, call->head_only, worker.http_date());
-    record_span(st, call->server_ctx, false, call->server_start_us, realtime_us(), 200, call->server_url, {}, {});
+    int status = 200;
+    // An empty tail is the marker for "the call failed and fallbacks are switched off"
+    // (hystrix.command.default.fallback.enabled=false): Hystrix then throws, the resource method
+    // fails and the client sees a 500.
+    if (tail.empty() && call->failed_without_fallback) {
+        status = 500;
+        append_response(&response, 500, "text/html", undertow_error_page(500), false, close, call->head_only, worker.http_date());
+    } else {
+        JsonStringList all;
+        all.reserve(tail.size() + 1);
+        all.emplace_back(std::move(call->hola_text));
+        for (auto& item : tail) all.emplace_back(std::move(item));
+        append_response(&response, 200, kJson, json_encode_string_list(all), true, close, call->head_only, worker.http_date());
+    }
+    record_span(st, call->server_ctx, false, call->server_start_us, realtime_us(), status, call->server_url, {}, {});
     if (call->deferred) {
         worker.complete(call->ref, response, close);
     } else {

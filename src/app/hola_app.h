@@ -82,6 +82,7 @@ class HolaApp final : public Application {
     void start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call);
     void send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCall>& call);
     void finish_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call, JsonStringList&& tail);
+    JsonStringList fallback_tail(ChainCall& call) const;
 
     // Tracing.
     void record_span(WorkerState& st, const TraceContext& ctx, bool client, int64_t start_us, int64_t end_us,

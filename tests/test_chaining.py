@@ -73,10 +73,14 @@ def test_connection_failures_are_retried_like_feign(hola_server, fake_aloha):
     elapsed = time.time() - t0
     assert 0.14 <= elapsed < 0.5, elapsed
     assert len(fake_aloha.snapshot()) == 2
-    # Two failures: 150 + 225 ms of pauses, still inside the 600 ms budget.
+    # Two failures: 150 + 225 ms of pauses, still inside the 600 ms budget. (A fresh server, so
+    # that no pooled keep-alive connection is involved: a request that dies on a reused
+    # connection is first repeated at once on a new one, like Apache HttpClient's own retry
+    # handler does underneath Feign.)
+    srv2 = hola_server(args=["--aloha-url", fake_aloha.url])
     fake_aloha.fail_first = 2
     t0 = time.time()
-    assert json.loads(chain(srv).body) == ["Hola de unknown"] + fake_aloha.payload
+    assert json.loads(chain(srv2).body) == ["Hola de unknown"] + fake_aloha.payload
     assert 0.37 <= time.time() - t0 < 0.6
     # HTTP error statuses are not retried.
     fake_aloha.mode = "500"
@@ -186,6 +190,18 @@ def test_client_gone_while_call_in_flight_is_harmless(hola_server, fake_aloha):
     c.close()
     time.sleep(0.5)
     assert client.get("127.0.0.1", srv.port, "/api/health").status == 200
+
+
+def test_fallback_disabled_turns_failures_into_500(hola_server, fake_aloha):
+    """hystrix.command.default.fallback.enabled=false: Hystrix throws instead of calling the fallback."""
+    fake_aloha.mode = "500"
+    srv = hola_server(args=["--aloha-url", fake_aloha.url, "-Dhystrix.command.default.fallback.enabled=false"])
+    r = client.get("127.0.0.1", srv.port, "/api/hola-chaining")
+    assert r.status == 500
+    fake_aloha.mode = "ok"
+    assert json.loads(chain(srv).body) == ["Hola de unknown"] + fake_aloha.payload
+    fake_aloha.payload = []
+    assert json.loads(chain(srv).body) == ["Hola de unknown"]  # an empty downstream list is not a failure
 
 
 def test_head_on_chaining(hola_server, fake_aloha):

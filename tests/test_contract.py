@@ -161,6 +161,10 @@ def test_query_string_and_trailing_slash(hola_server):
     assert get(srv, "/api/hola/").status == 200
     assert get(srv, "/api/holaa").status == 404
     assert get(srv, "/api/hol").status == 404
+    for bare in ("/api", "/api/"):
+        r = get(srv, bare)
+        assert r.status == 404 and r.header("Access-Control-Allow-Origin") == "*"  # still inside the JAX-RS mapping
+    assert get(srv, "/apix").header("Access-Control-Allow-Origin") is None
 
 
 def test_landing_page_is_the_reference_page(hola_server):
