@@ -44,6 +44,20 @@ def test_stream_pings_until_a_command_has_run(hola_server):
     c.close()
 
 
+def test_stream_for_an_http10_client_is_not_chunked(hola_server):
+    srv = hola_server()
+    c = client.Connection("127.0.0.1", srv.port, timeout=5)
+    c.send_raw(client.build_request("GET", "/hystrix.stream?delay=30", version="HTTP/1.0"))
+    data = b""
+    while data.count(b"ping: \n\n") < 3:
+        assert c._fill()
+        data = c.buf
+    head, _, body = data.partition(b"\r\n\r\n")
+    assert b"Transfer-Encoding" not in head and b"Connection: close" in head
+    assert body.startswith(b"ping: \n\nping: \n\n")  # raw events, no chunk-size lines
+    c.close()
+
+
 def test_stream_reports_command_and_pool_after_calls(hola_server, fake_aloha):
     srv = hola_server(args=["--aloha-url", fake_aloha.url], threads=1)
     for _ in range(3):
