@@ -255,7 +255,7 @@ void Connection::flush() {
     out_.clear();
     out_sent_ = 0;
     want_write_ = false;
-    if (close_after_write_ && !deferred_) {
+    if (close_after_write_ && !deferred_ && !streaming_) {
         close_now();
         return;
     }
