@@ -63,6 +63,19 @@ using namespace detail;
 
 namespace {
 
+void append_html_escaped(std::string* out, std::string_view s) {
+    for (char c : s) {
+        switch (c) {
+            case '<': out->append("&lt;"); break;
+            case '>': out->append("&gt;"); break;
+            case '&': out->append("&amp;"); break;
+            case '"': out->append("&quot;"); break;
+            case '\'': out->append("&#39;"); break;
+            default: out->push_back(c); break;
+        }
+    }
+}
+
 // One JAX-RS resource method as far as dispatch is concerned.
 enum class ApiRoute { kNone, kHola, kChaining, kHealth, kSwaggerJson, kSwaggerYaml };
 
@@ -168,9 +181,11 @@ Disposition HolaApp::handle(Worker& worker, Connection& conn, const RequestHead&
     if ((path.size() >= 5 && std::memcmp(path.data(), "/api/", 5) == 0) || path == "/api") {
         const ApiRoute route = match_api(path.substr(4));
         if (route == ApiRoute::kNone) {
+            // The message quotes the request URL and goes out as text/html: escape it, or any
+            // link to a non-existent /api path becomes a script-injection vector.
             std::string body = "RESTEASY003210: Could not find resource for full path: http://";
-            body.append(rq.host.empty() ? std::string_view("localhost") : rq.host);
-            body.append(rq.target);
+            append_html_escaped(&body, rq.host.empty() ? std::string_view("localhost") : rq.host);
+            append_html_escaped(&body, rq.target);
             append_response(&out, 404, kTextHtml, body, true, conn.closing(), rq.method == Method::kHead, worker.http_date());
             return Disposition::kDone;
         }

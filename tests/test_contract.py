@@ -155,6 +155,14 @@ def test_not_found_and_not_acceptable(hola_server):
     assert r.status == 406
 
 
+def test_error_page_does_not_reflect_markup(hola_server):
+    srv = hola_server()
+    r = get(srv, "/api/<script>alert(1)</script>", headers={"Host": "evil\"><img src=x>"})
+    assert r.status == 404
+    assert b"<script>" not in r.body and b"<img" not in r.body
+    assert b"&lt;script&gt;" in r.body
+
+
 def test_query_string_and_trailing_slash(hola_server):
     srv = hola_server()
     assert get(srv, "/api/hola?x=1&y=2").body == b"Hola de unknown"
