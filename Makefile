@@ -19,9 +19,11 @@ CXXFLAGS_COMMON := -std=c++17 -Wall -Wextra -Wshadow -Wno-missing-field-initiali
 CXXFLAGS_release := -O2 -g -DNDEBUG
 CXXFLAGS_asan    := -O1 -g -fsanitize=address,undefined -fno-omit-frame-pointer
 CXXFLAGS_tsan    := -O1 -g -fsanitize=thread -fno-omit-frame-pointer
+CXXFLAGS_cov     := -O0 -g --coverage
 LDFLAGS_release  :=
 LDFLAGS_asan     := -fsanitize=address,undefined
 LDFLAGS_tsan     := -fsanitize=thread
+LDFLAGS_cov      := --coverage
 
 CXXFLAGS := $(CXXFLAGS_COMMON) $(CXXFLAGS_$(VARIANT)) $(EXTRA_CXXFLAGS)
 LDFLAGS  := -pthread $(LDFLAGS_$(VARIANT)) $(EXTRA_LDFLAGS)
@@ -36,7 +38,7 @@ TEST_OBJ := $(patsubst tests/cpp/%.cc,$(BUILD)/obj/tests/%.o,$(TEST_SRC))
 
 TARGETS := $(BUILD)/hola $(BUILD)/hola-load $(BUILD)/hola-coldstart $(BUILD)/libhola.so $(BUILD)/hola_tests
 
-.PHONY: all static asan tsan test clean
+.PHONY: all static asan tsan cov test clean
 all: $(TARGETS)
 
 $(BUILD)/obj/%.o: src/%.cc
@@ -77,6 +79,9 @@ asan:
 	$(MAKE) VARIANT=asan CXX=$(SAN_CXX)
 tsan:
 	$(MAKE) VARIANT=tsan CXX=$(SAN_CXX)
+# gcov instrumentation under build/cov/; see tools/coverage.sh
+cov:
+	$(MAKE) VARIANT=cov CXX=$(SAN_CXX)
 
 test: $(BUILD)/hola_tests
 	$(BUILD)/hola_tests

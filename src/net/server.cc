@@ -37,11 +37,6 @@ inline void bump(std::atomic<uint64_t>& counter) {
 
 }  // namespace
 
-bool set_nonblocking(int fd) {
-    const int flags = fcntl(fd, F_GETFL, 0);
-    return flags >= 0 && fcntl(fd, F_SETFL, flags | O_NONBLOCK) == 0;
-}
-
 void set_nodelay(int fd) {
     const int one = 1;
     setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
@@ -394,14 +389,6 @@ bool Worker::stream_write(ConnRef ref, std::string_view bytes) {
     c->out_.append(bytes);
     c->flush();
     return c->fd_ >= 0;
-}
-
-void Worker::end_stream(ConnRef ref) {
-    Connection* c = lookup(ref);
-    if (!c || !c->streaming_) return;
-    c->streaming_ = false;  // no close notification for an orderly end
-    c->close_after_write_ = true;
-    c->flush();
 }
 
 void Worker::sweep_idle() {

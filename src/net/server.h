@@ -155,10 +155,9 @@ class Worker final : public EventHandler {
     // Completes a deferred request: appends `response` and resumes the connection. Returns
     // false when the connection no longer exists (the response is dropped).
     bool complete(ConnRef ref, std::string_view response, bool close_after);
-    // Writes to a streaming connection; false when it is gone. end_stream() closes it once the
-    // buffered bytes are out.
+    // Writes to a streaming connection; false when it is gone (or had to be dropped because the
+    // reader is not keeping up).
     bool stream_write(ConnRef ref, std::string_view bytes);
-    void end_stream(ConnRef ref);
     Connection* lookup(ConnRef ref);
 
     // Per-worker slot for application state (owned by the application).
@@ -220,8 +219,7 @@ class Server {
     bool started_ = false;
 };
 
-// Small helpers shared with the outbound client.
-bool set_nonblocking(int fd);
+// Small helper shared with the outbound client.
 void set_nodelay(int fd);
 
 }  // namespace hola

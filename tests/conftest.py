@@ -47,7 +47,7 @@ def pytest_report_header(config):
 
 
 def pytest_addoption(parser):
-    parser.addoption("--variant", default="release", choices=["release", "asan", "tsan", "static"],
+    parser.addoption("--variant", default="release", choices=["release", "asan", "tsan", "static", "cov"],
                      help="which build of the hola executable the black-box tests launch "
                           "(asan: AddressSanitizer+UBSan, tsan: ThreadSanitizer; SURVEY.md 5.2)")
 
@@ -132,6 +132,7 @@ class FakeAloha(_Recorder):
         self.payload = ["Aloha mai fake-aloha", "Olá de fake-ola", "Bonjour de fake-bonjour"]
         self.delay = 0.0
         self.fail_first = 0  # drop this many upcoming requests without answering
+        self.raw = []        # mode "raw": byte strings written one after the other
         fake = self
 
         class Handler(BaseHTTPRequestHandler):
@@ -173,6 +174,13 @@ class FakeAloha(_Recorder):
                 elif mode == "close":
                     self.close_connection = True
                     self.connection.close()
+                elif mode == "raw":
+                    # Arbitrary bytes (possibly in several writes), then the connection closes.
+                    for part in fake.raw:
+                        self.wfile.write(part)
+                        self.wfile.flush()
+                        time.sleep(0.02)
+                    self.close_connection = True
                 else:
                     self._reply(200, b"[]", "application/json")
 

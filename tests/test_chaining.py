@@ -192,6 +192,40 @@ def test_client_gone_while_call_in_flight_is_harmless(hola_server, fake_aloha):
     assert client.get("127.0.0.1", srv.port, "/api/health").status == 200
 
 
+def test_downstream_response_framings(hola_server, fake_aloha):
+    """The outbound client against the ways an HTTP/1.x server may frame its answer."""
+    srv = hola_server(args=["--aloha-url", fake_aloha.url, "-Dhystrix.command.default.circuitBreaker.enabled=false",
+                            "--feign-max-attempts", "1"])
+    good = ["Hola de unknown", "Aloha raw"]
+    body = b'["Aloha raw"]'
+    fake_aloha.mode = "raw"
+    # Body delimited by the connection closing (HTTP/1.0 style), arriving in two pieces.
+    fake_aloha.raw = [b"HTTP/1.0 200 OK\r\nContent-Type: application/json\r\n\r\n", body[:5], body[5:]]
+    assert json.loads(chain(srv).body) == good
+    # Response head split in the middle of a header line.
+    fake_aloha.raw = [b"HTTP/1.1 200 OK\r\nContent-Le", b"ngth: %d\r\nConnection: close\r\n\r\n" % len(body) + body]
+    assert json.loads(chain(srv).body) == good
+    # An interim 100 Continue before the real answer.
+    fake_aloha.raw = [b"HTTP/1.1 100 Continue\r\n\r\n", b"HTTP/1.1 200 OK\r\nContent-Length: %d\r\n\r\n" % len(body) + body]
+    assert json.loads(chain(srv).body) == good
+    # Keep-alive answer after which the server silently closes: the pooled connection is dropped
+    # when the close is noticed, and the next call simply opens a new one.
+    fake_aloha.raw = [b"HTTP/1.1 200 OK\r\nContent-Length: %d\r\n\r\n" % len(body) + body]
+    assert json.loads(chain(srv).body) == good
+    time.sleep(0.1)
+    assert json.loads(chain(srv).body) == good
+    # Things that must end in the fallback: no status line, a body far too large, a truncated
+    # body, a length that lies.
+    for raw in ([b"SMTP ready\r\n\r\n"],
+                [b"HTTP/1.1 200 OK\r\nContent-Length: 3000000\r\n\r\n", b"x" * 70000, b"x" * 70000] + [b"y" * 65536] * 20,
+                [b"HTTP/1.1 200 OK\r\nContent-Length: 50\r\n\r\n", body],
+                [b"HTTP/1.1 200 OK\r\nTransfer-Encoding: chunked\r\n\r\nZZ\r\n"]):
+        fake_aloha.raw = raw
+        assert json.loads(chain(srv).body) == ["Hola de unknown", FALLBACK], raw[0]
+    fake_aloha.mode = "ok"
+    assert json.loads(chain(srv).body) == ["Hola de unknown"] + fake_aloha.payload
+
+
 def test_fallback_disabled_turns_failures_into_500(hola_server, fake_aloha):
     """hystrix.command.default.fallback.enabled=false: Hystrix throws instead of calling the fallback."""
     fake_aloha.mode = "500"

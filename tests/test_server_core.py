@@ -96,10 +96,21 @@ def test_oversized_head_gets_431(hola_server):
         r = c.read_response()
         assert r.status == 431
         assert c.closed_by_peer()
-    # A large-but-allowed head still works (buffer growth path).
+    # A large-but-allowed head still works.
     with client.Connection("127.0.0.1", srv.port) as c:
         r = c.request("GET", "/api/hola", headers={"X-Filler": "b" * 3000})
         assert r.status == 200
+    # With the default 64 KiB limit the receive buffer has to grow several times, also when the
+    # head arrives in pieces, and the connection stays usable afterwards.
+    srv2 = hola_server()
+    with client.Connection("127.0.0.1", srv2.port) as c:
+        big = client.build_request("GET", "/api/hola", headers={"X-Filler": "c" * 40000})
+        for k in range(0, len(big), 9000):
+            c.send_raw(big[k:k + 9000])
+        assert c.read_response().body == HOLA
+        assert c.request("GET", "/api/health").body == b"I'm ok"
+        c.send_raw(client.build_request("GET", "/api/hola", headers={"X-Filler": "d" * 70000}))
+        assert c.read_response().status == 431
 
 
 def test_half_close_still_gets_the_answer(hola_server):
