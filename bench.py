@@ -153,8 +153,13 @@ def main() -> int:
     if dist is not None:
         dist.barrier()
     t0 = time.monotonic()
-    threads = [threading.Thread(target=run_instance, args=(i, slices[i % len(slices)], args.steps, args.warmup, args.mode,
-                                                           args.max_cpus, args.server_share, results)) for i in my_indices]
+    def guarded(i: int) -> None:
+        try:
+            run_instance(i, slices[i % len(slices)], args.steps, args.warmup, args.mode, args.max_cpus, args.server_share, results)
+        except Exception as exc:  # noqa: BLE001 - reported below, on every rank
+            results[i] = {"error": "%s: %s" % (type(exc).__name__, exc)}
+
+    threads = [threading.Thread(target=guarded, args=(i,)) for i in my_indices]
     for t in threads:
         t.start()
     for t in threads:
@@ -164,9 +169,20 @@ def main() -> int:
         dist.barrier()
     clocks = sampler.stop() if sampler else None
 
-    missing = [i for i in my_indices if i not in results]
-    if missing:
-        print("bench: instance(s) %s failed" % missing, file=sys.stderr)
+    # A failed instance (a request error, a server that did not start) invalidates the whole run.
+    # Every rank learns about it before anyone leaves, so that nobody is left waiting in a collective.
+    missing = [i for i in my_indices if i not in results or "error" in results[i]]
+    failed = 1.0 if missing else 0.0
+    if dist is not None:
+        import torch
+        flag = torch.tensor([failed], dtype=torch.float64)
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+        failed = float(flag[0])
+    if failed:
+        for i in missing:
+            print("bench: instance %d failed: %s" % (i, results.get(i, {}).get("error", "no result")), file=sys.stderr)
+        if dist is not None:
+            dist.destroy_process_group()
         return 1
 
     # Aggregate over local instances, then over ranks.

@@ -17,20 +17,47 @@ FALLBACK = "Aloha response (fallback)"
 
 
 class FakeDns:
-    """Answers A queries from a dict; everything else is NXDOMAIN. Optionally slow or silent."""
+    """Answers A queries from a dict; everything else is NXDOMAIN. Optionally slow, silent, or
+    truncating (TC bit over UDP, full answer over TCP on the same port)."""
 
     def __init__(self, records):
         self.records = {k.lower(): v for k, v in records.items()}
         self.delay = 0.0
         self.silent = False
+        self.truncate_udp = False
         self.queries = []
+        self.tcp_queries = []
         self.sock = socket.socket(socket.AF_INET, socket.SOCK_DGRAM)
         self.sock.bind(("127.0.0.1", 0))
         self.port = self.sock.getsockname()[1]
         self.sock.settimeout(0.2)
+        self.tcp = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+        self.tcp.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+        self.tcp.bind(("127.0.0.1", self.port))
+        self.tcp.listen(16)
+        self.tcp.settimeout(0.2)
         self._stop = False
         self.thread = threading.Thread(target=self._serve, daemon=True)
         self.thread.start()
+        self.tcp_thread = threading.Thread(target=self._serve_tcp, daemon=True)
+        self.tcp_thread.start()
+
+    def _answer(self, data, truncated=False):
+        qid = data[:2]
+        pos, labels = 12, []
+        while data[pos]:
+            n = data[pos]
+            labels.append(data[pos + 1:pos + 1 + n].decode())
+            pos += 1 + n
+        name = ".".join(labels).lower()
+        question = data[12:pos + 5]
+        ip = self.records.get(name)
+        if truncated:
+            return name, qid + b"\x83\x80" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
+        if ip is None:
+            return name, qid + b"\x81\x83" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
+        answer = b"\xc0\x0c" + struct.pack(">HHIH", 1, 1, 30, 4) + socket.inet_aton(ip)
+        return name, qid + b"\x81\x80" + b"\x00\x01\x00\x01\x00\x00\x00\x00" + question + answer
 
     def _serve(self):
         while not self._stop:
@@ -40,31 +67,42 @@ class FakeDns:
                 continue
             except OSError:
                 return
-            qid = data[:2]
-            pos, labels = 12, []
-            while data[pos]:
-                n = data[pos]
-                labels.append(data[pos + 1:pos + 1 + n].decode())
-                pos += 1 + n
-            name = ".".join(labels).lower()
-            question = data[12:pos + 5]
+            name, reply = self._answer(data, truncated=self.truncate_udp)
             self.queries.append(name)
             if self.silent:
                 continue
             if self.delay:
                 time.sleep(self.delay)
-            ip = self.records.get(name)
-            if ip is None:
-                reply = qid + b"\x81\x83" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
-            else:
-                answer = b"\xc0\x0c" + struct.pack(">HHIH", 1, 1, 30, 4) + socket.inet_aton(ip)
-                reply = qid + b"\x81\x80" + b"\x00\x01\x00\x01\x00\x00\x00\x00" + question + answer
             self.sock.sendto(reply, addr)
+
+    def _serve_tcp(self):
+        while not self._stop:
+            try:
+                conn, _ = self.tcp.accept()
+            except socket.timeout:
+                continue
+            except OSError:
+                return
+            with conn:
+                conn.settimeout(2)
+                try:
+                    head = conn.recv(2)
+                    (n,) = struct.unpack(">H", head)
+                    data = b""
+                    while len(data) < n:
+                        data += conn.recv(n - len(data))
+                    name, reply = self._answer(data)
+                    self.tcp_queries.append(name)
+                    conn.sendall(struct.pack(">H", len(reply)) + reply)
+                except (OSError, struct.error):
+                    pass
 
     def stop(self):
         self._stop = True
         self.thread.join(timeout=2)
+        self.tcp_thread.join(timeout=2)
         self.sock.close()
+        self.tcp.close()
 
 
 @pytest.fixture
@@ -164,4 +202,23 @@ def test_zipkin_host_is_resolved_the_same_way(hola_server, fake_zipkin, fake_dns
 
 def test_resolve_flag_pins_a_name(hola_server, fake_aloha):
     srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port, "--resolve", "aloha=127.0.0.1"])
+    assert chain(srv)[1:] == fake_aloha.payload
+
+
+def test_truncated_udp_answer_is_retried_over_tcp(hola_server, fake_aloha, fake_dns, tmp_path):
+    dns = fake_dns({"aloha.msa.svc.cluster.local": "127.0.0.1"})
+    dns.truncate_udp = True
+    srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port], env=dns_env(tmp_path, dns))
+    assert chain(srv)[1:] == fake_aloha.payload
+    assert dns.tcp_queries == ["aloha.msa.svc.cluster.local"]
+
+
+def test_second_name_server_is_tried_when_the_first_is_dead(hola_server, fake_aloha, fake_dns, tmp_path):
+    dns = fake_dns({"aloha.msa.svc.cluster.local": "127.0.0.1"})
+    env = dns_env(tmp_path, dns, options="ndots:5 timeout:1 attempts:2")
+    # 127.0.0.2 answers nothing on that port (ICMP unreachable on loopback), the second entry is the fake.
+    (tmp_path / "resolv.conf").write_text("nameserver 127.0.0.2\nnameserver 127.0.0.1\nsearch msa.svc.cluster.local\n"
+                                          "options ndots:5 timeout:1 attempts:2\n")
+    srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port,
+                            "-Dhystrix.command.default.execution.isolation.thread.timeoutInMilliseconds=3000"], env=env)
     assert chain(srv)[1:] == fake_aloha.payload
