@@ -123,6 +123,7 @@ class LoadThread {
         request_ += "Host: " + opt.host + ":" + std::to_string(opt.port) + "\r\n";
         for (const auto& h : opt.headers) request_ += h + "\r\n";
         request_ += "\r\n";
+        for (int k = 0; k < 16; ++k) request_batch_ += request_;  // 16 = the largest pipeline depth
     }
 
     void run() {
@@ -265,15 +266,17 @@ class LoadThread {
     }
 
     void flush_writes(Conn& c, int64_t now) {
+        // All queued requests go out in one send(): request_batch_ holds 16 copies back to back,
+        // and sent_off is the position inside the first of the still-queued copies.
         while (c.to_write > 0) {
-            const ssize_t n = send(c.fd, request_.data() + c.sent_off, request_.size() - c.sent_off, MSG_NOSIGNAL);
+            const size_t len = static_cast<size_t>(c.to_write) * request_.size() - c.sent_off;
+            const ssize_t n = send(c.fd, request_batch_.data() + c.sent_off, len, MSG_NOSIGNAL);
             if (n > 0) {
-                c.sent_off += static_cast<size_t>(n);
-                if (c.sent_off == request_.size()) {
-                    c.sent_off = 0;
-                    --c.to_write;
-                    ++c.in_flight;
-                }
+                const size_t progressed = c.sent_off + static_cast<size_t>(n);
+                const int completed = static_cast<int>(progressed / request_.size());
+                c.sent_off = progressed % request_.size();
+                c.to_write -= completed;
+                c.in_flight += completed;
                 continue;
             }
             if (n < 0 && errno == EINTR) continue;
@@ -400,7 +403,13 @@ class LoadThread {
             std::memmove(c.rbuf, c.rbuf + pos, c.rlen - pos);
             c.rlen -= pos;
         }
-        return true;
+        // Refill the pipeline / send what has become due.
+        if (conn_period_ns_ == 0) {
+            fill_closed_loop(c, now);
+        } else if (c.next_due_ns <= now) {
+            schedule_open_loop(c, now);
+        }
+        return c.fd >= 0 && c.state == Conn::kReady;
     }
 
     uint64_t& interval_bytes(int64_t now) { return intervals_[interval_index(now)].bytes; }
@@ -435,13 +444,8 @@ class LoadThread {
             reopen(c, now);
             return false;
         }
-        if (conn_period_ns_ == 0) {
-            fill_closed_loop(c, now);
-            if (c.fd < 0 || c.state != Conn::kReady) return false;
-        } else if (c.next_due_ns <= now) {
-            schedule_open_loop(c, now);
-            if (c.fd < 0 || c.state != Conn::kReady) return false;
-        }
+        // The replacement request is written by parse() once every response in the receive
+        // buffer has been handled, so that a pipelining client refills with one send().
         return true;
     }
 
@@ -470,6 +474,7 @@ class LoadThread {
     int64_t last_event_ns_ = 0;
     int epfd_ = -1;
     std::string request_;
+    std::string request_batch_;
     std::vector<Conn> conns_;
     std::vector<Interval> intervals_;
     Errors errors_;
