@@ -27,13 +27,23 @@ class FakeDns:
         self.truncate_udp = False
         self.queries = []
         self.tcp_queries = []
-        self.sock = socket.socket(socket.AF_INET, socket.SOCK_DGRAM)
-        self.sock.bind(("127.0.0.1", 0))
-        self.port = self.sock.getsockname()[1]
+        # UDP and TCP on the same port number; another socket may hold the TCP side of the port
+        # the kernel picked for UDP, so try again until both can be had.
+        for _ in range(50):
+            self.sock = socket.socket(socket.AF_INET, socket.SOCK_DGRAM)
+            self.sock.bind(("127.0.0.1", 0))
+            self.port = self.sock.getsockname()[1]
+            self.tcp = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+            self.tcp.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+            try:
+                self.tcp.bind(("127.0.0.1", self.port))
+                break
+            except OSError:
+                self.sock.close()
+                self.tcp.close()
+        else:
+            raise RuntimeError("no port free for both UDP and TCP")
         self.sock.settimeout(0.2)
-        self.tcp = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
-        self.tcp.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
-        self.tcp.bind(("127.0.0.1", self.port))
         self.tcp.listen(16)
         self.tcp.settimeout(0.2)
         self._stop = False
