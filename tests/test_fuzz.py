@@ -91,6 +91,46 @@ def test_mutated_requests_never_take_the_server_down(hola_server):
     assert srv.stop() == 0
 
 
+def test_random_valid_pipelines_match_a_model(hola_server, fake_aloha):
+    """Model-based check of the connection state machine: random sequences of *valid* requests,
+    pipelined on one connection and cut into random TCP segments, must produce exactly the
+    responses the same requests produce one at a time, in order. Includes deferred requests
+    (the downstream call) and requests with bodies in the middle of the pipeline."""
+    fake_aloha.delay = 0.002
+    srv = hola_server(args=["--aloha-url", fake_aloha.url], threads=2)
+    chained = ('["Hola de unknown",' + ",".join('"%s"' % p for p in fake_aloha.payload) + "]").encode()
+    menu = [
+        (client.build_request("GET", "/api/hola"), (200, b"Hola de unknown")),
+        (client.build_request("GET", "/api/hola?x=%d" % 7), (200, b"Hola de unknown")),
+        (client.build_request("GET", "/api/health"), (200, b"I'm ok")),
+        (client.build_request("HEAD", "/api/hola"), (200, b"")),
+        (client.build_request("GET", "/api/hola-chaining"), (200, chained)),
+        (client.build_request("POST", "/api/hola", body=b"GET /api/health HTTP/1.1\r\n\r\n"), (405, b"")),
+        (b"PUT /api/health HTTP/1.1\r\nHost: x\r\nTransfer-Encoding: chunked\r\n\r\n3\r\nabc\r\n0\r\n\r\n", (405, b"")),
+        (client.build_request("GET", "/api/none"), (404, None)),
+        (client.build_request("GET", "/"), (200, None)),
+        (client.build_request("GET", "/api/hola", headers={"Accept": "image/png"}), (406, None)),
+        (client.build_request("OPTIONS", "/api/health"), (200, b"HEAD, GET, OPTIONS")),
+    ]
+    rng = random.Random(4242)
+    for round_no in range(25):
+        picks = [rng.choice(menu) for _ in range(rng.randint(1, 30))]
+        wire = b"".join(p[0] for p in picks)
+        with client.Connection("127.0.0.1", srv.port, timeout=10) as c:
+            pos = 0
+            while pos < len(wire):
+                step = rng.choice([1, 2, 3, 7, 20, 100, 1000, len(wire)])
+                c.send_raw(wire[pos:pos + step])
+                pos += step
+            for i, (raw, (status, body)) in enumerate(picks):
+                r = c.read_response(head_only=raw.startswith(b"HEAD"))
+                assert r.status == status, (round_no, i, raw[:40], r.status)
+                if body is not None:
+                    assert r.body == body, (round_no, i, raw[:40], r.body)
+            # Nothing extra was produced, and the connection is still in sync.
+            assert c.request("GET", "/api/health").body == b"I'm ok"
+
+
 def test_random_bytes_and_huge_lines(hola_server):
     srv = hola_server(threads=1, args=["--max-header-bytes", "4096"])
     rng = random.Random(7)
