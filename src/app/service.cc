@@ -41,6 +41,8 @@ std::string usage_text() {
            "  --deltaspike-properties FILE  extra config source at ordinal 100 (META-INF/apache-deltaspike.properties)\n"
            "  --webjars-dir DIR           directory served under /webjars/ (Swagger-UI assets)\n"
            "  --idle-timeout MS           close keep-alive connections idle for MS (default: never)\n"
+           "  --drain-linger-ms N         on SIGTERM keep answering on open connections for N ms (each answer says\n"
+           "                              \"Connection: close\") before closing the idle ones (default 100)\n"
            "  --spin-us N                 keep polling for N us after the last event before sleeping (default 0;\n"
            "                              for pinned, dedicated cores: trades idle CPU for lower latency)\n"
            "  --max-header-bytes N        request head limit (default 65536)\n"
@@ -141,6 +143,9 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
         } else if (a == "--idle-timeout") {
             if (!value(&v) || !parse_uint(v, 86400000, &n)) return fail("--idle-timeout needs milliseconds");
             cfg->server.idle_timeout_ms = static_cast<int>(n);
+        } else if (a == "--drain-linger-ms") {
+            if (!value(&v) || !parse_uint(v, 600000, &n)) return fail("--drain-linger-ms needs milliseconds");
+            cfg->server.drain_linger_ms = static_cast<int>(n);
         } else if (a == "--spin-us") {
             if (!value(&v) || !parse_uint(v, 1000000, &n)) return fail("--spin-us needs microseconds");
             cfg->server.spin_us = static_cast<int>(n);

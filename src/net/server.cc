@@ -414,18 +414,32 @@ void Worker::begin_drain() {
     }
     app_->on_worker_stop(*this);
     for (auto& c : conns_) {
-        if (c->fd_ < 0) continue;
-        if (c->streaming_) {
-            c->close_now();
-        } else if (!c->deferred_ && c->out_sent_ >= c->out_.size()) {
-            c->close_now();  // idle keep-alive connection
-        } else {
-            c->close_after_write_ = true;
-        }
+        if (c->fd_ >= 0 && c->streaming_) c->close_now();
     }
     if (open_count_ == 0) {
         loop_.stop();
         return;
+    }
+    // Keep-alive connections are not cut off at once: a client may be writing its next request
+    // this very moment, and closing under it turns a clean shutdown into a failed request. For
+    // a short linger period every request still gets its answer - marked "Connection: close",
+    // because draining() is now true - and only connections that stayed silent are closed after
+    // it. A busy client is therefore moved to another instance without seeing an error.
+    auto close_idle = [this] {
+        for (auto& c : conns_) {
+            if (c->fd_ < 0) continue;
+            if (!c->deferred_ && c->out_sent_ >= c->out_.size()) {
+                c->close_now();
+            } else {
+                c->close_after_write_ = true;
+            }
+        }
+    };
+    if (options_.drain_linger_ms <= 0) {
+        close_idle();
+        if (open_count_ == 0) return;  // release() has stopped the loop
+    } else {
+        loop_.add_timer(loop_.now_ns() + static_cast<int64_t>(options_.drain_linger_ms) * 1000000, close_idle);
     }
     loop_.add_timer(loop_.now_ns() + static_cast<int64_t>(options_.shutdown_grace_ms) * 1000000,
                     [this] { loop_.stop(); });

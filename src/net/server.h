@@ -114,7 +114,8 @@ struct ServerOptions {
     size_t max_header_bytes = 65536;  // request line + headers
     bool reuse_port = true;           // false: worker 0 accepts and deals connections round-robin
     std::vector<int> cpu_affinity;    // optional: worker i is pinned to cpu_affinity[i % size]
-    int shutdown_grace_ms = 5000;
+    int shutdown_grace_ms = 5000;     // in-flight work gets this long to finish after SIGTERM
+    int drain_linger_ms = 100;        // idle keep-alive connections stay answerable this long (see begin_drain)
     int idle_timeout_ms = 0;          // 0: never close idle keep-alive connections
     int spin_us = 0;                  // busy-poll window after the last event (EventLoop::set_spin_ns)
 };

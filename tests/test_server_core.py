@@ -173,6 +173,31 @@ def test_graceful_shutdown_finishes_in_flight_and_exits_zero(hola_server):
         assert c.closed_by_peer()
 
 
+def test_rolling_restart_loses_no_request(hola_server):
+    """Zero-downtime replacement: a second instance joins the same port (SO_REUSEPORT), the first
+    gets SIGTERM while 16 keep-alive clients hammer the port. The old instance answers what it has
+    received, tells each client to reconnect (Connection: close) and exits 0; the clients land on
+    the new instance; nobody sees a failed request."""
+    import json
+    import subprocess
+    from hola_b200 import paths
+    old = hola_server(threads=2)
+    load = subprocess.Popen([str(paths().hola_load), "--json", "-c", "16", "-d", "3", "-w", "0", "-t", "2", "--expect-body",
+                             "Hola de unknown", "http://127.0.0.1:%d/api/hola" % old.port], stdout=subprocess.PIPE, text=True)
+    time.sleep(1.0)
+    new = hola_server(args=["-Dswarm.http.port=%d" % old.port], threads=2)
+    assert new.port == old.port
+    time.sleep(0.3)
+    assert old.stop() == 0
+    out = load.communicate(timeout=30)[0]
+    rep = json.loads(out.strip().splitlines()[-1])
+    assert rep["errors"]["total"] == 0, rep["errors"]
+    assert rep["reconnects"] >= 1  # clients really were moved over
+    assert rep["requests"] > 1000
+    # Throughput did not drop to zero in any interval.
+    assert min(i["requests"] for i in rep["intervals"]) > 0
+
+
 def test_date_header_is_current_and_well_formed(hola_server):
     import email.utils
     srv = hola_server()
