@@ -270,7 +270,7 @@ void HystrixCommand::record_locked(int64_t now_ms, HystrixEvent e) {
 
 HystrixCommand::Admission HystrixCommand::admit(int64_t now_ms) {
     std::lock_guard<std::mutex> lock(mu_);
-    executed_once_ = true;
+    executed_once_.store(true, std::memory_order_relaxed);
     if (!allow_request_locked(now_ms)) {
         record_locked(now_ms, HystrixEvent::kShortCircuited);
         record_locked(now_ms, cfg_.fallback_enabled ? HystrixEvent::kFallbackSuccess : HystrixEvent::kFallbackMissing);

@@ -23,6 +23,7 @@
 #pragma once
 
 #include <array>
+#include <atomic>
 #include <cstdint>
 #include <mutex>
 #include <string>
@@ -197,7 +198,7 @@ class HystrixCommand {
     HealthCounts health(int64_t now_ms);
     CommandSnapshot snapshot(int64_t now_ms);
     PoolSnapshot pool_snapshot(int64_t now_ms);
-    bool has_executed() const { return executed_once_; }
+    bool has_executed() const { return executed_once_.load(std::memory_order_relaxed); }
 
  private:
     bool allow_request_locked(int64_t now_ms);
@@ -221,7 +222,7 @@ class HystrixCommand {
     int active_ = 0;
     int largest_active_ = 0;
     int64_t completed_tasks_ = 0;
-    bool executed_once_ = false;
+    std::atomic<bool> executed_once_{false};  // read by the metrics stream without the lock
 };
 
 // Rendering of the two `data:` payloads of /hystrix.stream with Hystrix 1.5.1's field names.
