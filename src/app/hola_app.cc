@@ -106,16 +106,16 @@ HolaApp::HolaApp(AppOptions options, GreetingService* greeting, Tracer* tracer, 
                             "\r\nAccept: */*\r\nConnection: keep-alive\r\nUser-Agent: hola-b200\r\n";
 }
 
-HolaApp::~HolaApp() {
-    // The workers (and their event loops) are gone by now; see Service::stop().
-    for (WorkerState* st : states_) delete st;
-}
+// The per-worker states die with the application; the workers (and their event loops) are gone
+// by then, see Service::stop() and on_worker_exit().
+HolaApp::~HolaApp() = default;
 
 void HolaApp::on_worker_start(Worker& worker) {
-    auto* st = new WorkerState();
+    WorkerState* st;
     {
         std::lock_guard<std::mutex> lock(states_mu_);
-        states_.push_back(st);
+        states_.emplace_back(new WorkerState());
+        st = states_.back().get();
     }
     st->worker = &worker;
     if (tracer_->enabled()) st->ring = tracer_->register_producer();

@@ -97,7 +97,7 @@ class HolaApp final : public Application {
     Resolver* resolver_;
     HystrixCommand command_;
     std::mutex states_mu_;
-    std::vector<WorkerState*> states_;  // one per worker thread, freed with the application
+    std::vector<std::unique_ptr<WorkerState>> states_;  // one per worker thread
     std::atomic<int> stream_connections_{0};
     std::string aloha_request_prefix_;  // request line + fixed headers, B3 headers are appended
     std::string aloha_url_;             // for the client span's http.url tag
