@@ -27,7 +27,8 @@ std::string usage_text() {
            "\n"
            "Options:\n"
            "  --conf FILE                 same as -Dconf=FILE\n"
-           "  --port N, --bind ADDR       same as the swarm.* definitions (port 0: pick a free one)\n"
+           "  --port N, --bind ADDR       same as the swarm.* definitions (port 0: pick a free one; --bind :: listens\n"
+           "                              on IPv6 and IPv4)\n"
            "  --threads N                 event-loop threads (default: one per available CPU)\n"
            "  --cpus LIST                 pin thread i to the i-th CPU of LIST (e.g. 0,1,2,3 or 0-3)\n"
            "  --accept-mode MODE          reuseport (default; one listener per thread) | rr (one acceptor, round-robin)\n"

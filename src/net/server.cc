@@ -276,23 +276,41 @@ std::string_view Worker::http_date() {
 }
 
 bool Worker::open_listener(std::string* error) {
-    const int fd = socket(AF_INET, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
+    // An address with a colon is IPv6; "::" then means dual stack (IPv4 clients arrive as
+    // v4-mapped addresses on the same socket).
+    const bool v6 = options_.bind_address.find(':') != std::string::npos;
+    sockaddr_storage storage{};
+    socklen_t addr_len = 0;
+    if (v6) {
+        auto* a = reinterpret_cast<sockaddr_in6*>(&storage);
+        a->sin6_family = AF_INET6;
+        a->sin6_port = htons(options_.port);
+        addr_len = sizeof *a;
+        if (inet_pton(AF_INET6, options_.bind_address.c_str(), &a->sin6_addr) != 1) {
+            *error = "bad bind address: " + options_.bind_address;
+            return false;
+        }
+    } else {
+        auto* a = reinterpret_cast<sockaddr_in*>(&storage);
+        a->sin_family = AF_INET;
+        a->sin_port = htons(options_.port);
+        addr_len = sizeof *a;
+        if (inet_pton(AF_INET, options_.bind_address.c_str(), &a->sin_addr) != 1) {
+            *error = "bad bind address: " + options_.bind_address;
+            return false;
+        }
+    }
+    const int fd = socket(v6 ? AF_INET6 : AF_INET, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
     if (fd < 0) {
         *error = std::string("socket: ") + std::strerror(errno);
         return false;
     }
     const int one = 1;
+    const int zero = 0;
     setsockopt(fd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
     if (options_.reuse_port) setsockopt(fd, SOL_SOCKET, SO_REUSEPORT, &one, sizeof one);
-    sockaddr_in addr{};
-    addr.sin_family = AF_INET;
-    addr.sin_port = htons(options_.port);
-    if (inet_pton(AF_INET, options_.bind_address.c_str(), &addr.sin_addr) != 1) {
-        *error = "bad bind address: " + options_.bind_address;
-        close(fd);
-        return false;
-    }
-    if (bind(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) != 0) {
+    if (v6) setsockopt(fd, IPPROTO_IPV6, IPV6_V6ONLY, &zero, sizeof zero);
+    if (bind(fd, reinterpret_cast<sockaddr*>(&storage), addr_len) != 0) {
         *error = "bind " + options_.bind_address + ":" + std::to_string(options_.port) + ": " + std::strerror(errno);
         close(fd);
         return false;
@@ -504,10 +522,11 @@ bool Server::start(std::string* error) {
             return false;
         }
         if (i == 0) {
-            sockaddr_in addr{};
+            sockaddr_storage addr{};
             socklen_t len = sizeof addr;
             getsockname(w.listen_fd_, reinterpret_cast<sockaddr*>(&addr), &len);
-            bound_port_ = ntohs(addr.sin_port);
+            bound_port_ = addr.ss_family == AF_INET6 ? ntohs(reinterpret_cast<sockaddr_in6*>(&addr)->sin6_port)
+                                                     : ntohs(reinterpret_cast<sockaddr_in*>(&addr)->sin_port);
             options_.port = bound_port_;  // later listeners join the same (possibly ephemeral) port
         }
     }

@@ -155,6 +155,31 @@ def test_accept_modes(hola_server, mode):
             c.close()
 
 
+def test_dual_stack_listener(hola_server):
+    """`--bind ::` listens on IPv6 and IPv4 at once (the reference's container binds 0.0.0.0 only;
+    IPv6-only pods need this)."""
+    try:
+        probe = socket.socket(socket.AF_INET6)
+        probe.bind(("::1", 0))
+        probe.close()
+    except OSError:
+        pytest.skip("no IPv6 loopback on this machine")
+    srv = hola_server(args=["--bind", "::"])
+    for family, host in ((socket.AF_INET6, "::1"), (socket.AF_INET, "127.0.0.1")):
+        s = socket.socket(family, socket.SOCK_STREAM)
+        s.settimeout(5)
+        s.connect((host, srv.port))
+        s.sendall(client.build_request("GET", "/api/hola", headers={"Connection": "close"}))
+        data = b""
+        while True:
+            chunk = s.recv(4096)
+            if not chunk:
+                break
+            data += chunk
+        s.close()
+        assert data.startswith(b"HTTP/1.1 200 OK") and data.endswith(HOLA), (host, data)
+
+
 def test_idle_timeout(hola_server):
     srv = hola_server(args=["--idle-timeout", "300"])
     with client.Connection("127.0.0.1", srv.port) as c:
