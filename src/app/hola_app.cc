@@ -91,6 +91,16 @@ ApiRoute match_api(std::string_view sub) {
 
 }  // namespace
 
+namespace {
+
+// host:port as it appears in URLs and Host headers (IPv6 literals go in brackets).
+std::string authority_of(const AppOptions& o) {
+    const bool v6_literal = o.aloha_host.find(':') != std::string::npos;
+    return (v6_literal ? "[" + o.aloha_host + "]" : o.aloha_host) + ":" + std::to_string(o.aloha_port);
+}
+
+}  // namespace
+
 HolaApp::HolaApp(AppOptions options, GreetingService* greeting, Tracer* tracer, Resolver* resolver)
     : options_(std::move(options)),
       greeting_(greeting),
@@ -98,9 +108,9 @@ HolaApp::HolaApp(AppOptions options, GreetingService* greeting, Tracer* tracer, 
       resolver_(resolver),
       // Key names as HystrixFeign derives them: command = Feign.configKey(type, method),
       // group and thread pool = the target's name, which for a hard-coded target is its URL.
-      command_("AlohaService#aloha()", "http://" + options_.aloha_host + ":" + std::to_string(options_.aloha_port) + "/",
-               "http://" + options_.aloha_host + ":" + std::to_string(options_.aloha_port) + "/", options_.breaker) {
-    const std::string authority = options_.aloha_host + ":" + std::to_string(options_.aloha_port);
+      command_("AlohaService#aloha()", "http://" + authority_of(options_) + "/", "http://" + authority_of(options_) + "/",
+               options_.breaker) {
+    const std::string authority = authority_of(options_);
     aloha_url_ = "http://" + authority + options_.aloha_path;
     aloha_request_prefix_ = "GET " + options_.aloha_path + " HTTP/1.1\r\nHost: " + authority +
                             "\r\nAccept: */*\r\nConnection: keep-alive\r\nUser-Agent: hola-b200\r\n";

@@ -120,11 +120,10 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
             if (!value(&v) || !parse_uint(v, 100, &n) || n == 0) return fail("--feign-max-attempts needs a number >= 1");
             cfg->app.feign_max_attempts = static_cast<int>(n);
         } else if (a == "--resolve") {
-            if (!value(&v)) return fail("--resolve needs NAME=IPV4");
+            if (!value(&v)) return fail("--resolve needs NAME=ADDRESS");
             const size_t eq = v.find('=');
-            in_addr addr;
-            if (eq == std::string::npos || eq == 0 || inet_pton(AF_INET, v.substr(eq + 1).c_str(), &addr) != 1)
-                return fail("--resolve needs NAME=IPV4");
+            if (eq == std::string::npos || eq == 0 || IpAddress::parse(v.substr(eq + 1)).family == 0)
+                return fail("--resolve needs NAME=ADDRESS (an IPv4 or IPv6 address)");
             cfg->static_hosts.emplace_back(v.substr(0, eq), v.substr(eq + 1));
         } else if (a == "--zipkin-url") {
             if (!value(&v)) return fail("--zipkin-url needs a value");
@@ -252,11 +251,7 @@ bool Service::start(std::string* error) {
     tracer_.reset(new Tracer(zipkin_url, "hola", config_.zipkin_flush_ms));
     if (!tracer_->error().empty()) log("WARN", tracer_->error() + " - tracing disabled");
     dns_.reset(new Resolver());
-    for (const auto& kv : config_.static_hosts) {
-        in_addr addr;
-        inet_pton(AF_INET, kv.second.c_str(), &addr);
-        dns_->set_static(kv.first, addr.s_addr);
-    }
+    for (const auto& kv : config_.static_hosts) dns_->set_static(kv.first, IpAddress::parse(kv.second));
     app_.reset(new HolaApp(config_.app, greeting_.get(), tracer_.get(), dns_.get()));
     server_.reset(new Server(config_.server, app_.get()));
     if (!server_->start(error)) {

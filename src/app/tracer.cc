@@ -26,14 +26,27 @@ bool parse_http_url(const std::string& url, std::string* host, uint16_t* port, s
     if (authority.empty()) return false;
     *path = slash == std::string::npos ? "" : url.substr(slash);
     while (!path->empty() && path->back() == '/') path->pop_back();
-    const size_t colon = authority.rfind(':');
-    if (colon == std::string::npos) {
-        *host = authority;
-        *port = 80;
-        return true;
+    std::string p;
+    if (authority[0] == '[') {  // IPv6 literal: http://[fd00::1]:8080/
+        const size_t close = authority.find(']');
+        if (close == std::string::npos || close == 1) return false;
+        *host = authority.substr(1, close - 1);
+        if (close + 1 == authority.size()) {
+            *port = 80;
+            return true;
+        }
+        if (authority[close + 1] != ':') return false;
+        p = authority.substr(close + 2);
+    } else {
+        const size_t colon = authority.rfind(':');
+        if (colon == std::string::npos) {
+            *host = authority;
+            *port = 80;
+            return true;
+        }
+        *host = authority.substr(0, colon);
+        p = authority.substr(colon + 1);
     }
-    *host = authority.substr(0, colon);
-    const std::string p = authority.substr(colon + 1);
     if (host->empty() || p.empty() || p.size() > 5) return false;
     unsigned v = 0;
     for (char c : p) {
@@ -214,15 +227,15 @@ bool wait_fd(int fd, short events, int timeout_ms) {
 }
 
 int connect_with_timeout(const std::string& host, uint16_t port, int timeout_ms) {
-    sockaddr_in addr{};
-    addr.sin_family = AF_INET;
-    if (resolve_ipv4(host, DnsConfig::load_system(), &addr.sin_addr.s_addr, timeout_ms) != DnsStatus::kOk) return -1;
-    addr.sin_port = htons(port);
-    const int fd = socket(AF_INET, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
+    IpAddress address;
+    if (resolve_address(host, DnsConfig::load_system(), &address, timeout_ms) != DnsStatus::kOk) return -1;
+    sockaddr_storage addr;
+    const socklen_t addr_len = address.to_sockaddr(port, &addr);
+    const int fd = socket(address.family == AF_INET6 ? AF_INET6 : AF_INET, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
     if (fd < 0) return -1;
     const int one = 1;
     setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
-    if (connect(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) != 0) {
+    if (connect(fd, reinterpret_cast<sockaddr*>(&addr), addr_len) != 0) {
         if (errno != EINPROGRESS || !wait_fd(fd, POLLOUT, timeout_ms)) {
             close(fd);
             return -1;
@@ -261,7 +274,8 @@ bool Tracer::post(const std::string& body) {
     const bool stopping = stopping_.load(std::memory_order_relaxed);
     const int connect_timeout_ms = stopping ? 500 : 10000;
     const int io_timeout_ms = stopping ? 1000 : 60000;
-    std::string head = "POST " + path_ + " HTTP/1.1\r\nHost: " + host_ + ":" + std::to_string(port_) +
+    const std::string host_for_header = host_.find(':') != std::string::npos ? "[" + host_ + "]" : host_;
+    std::string head = "POST " + path_ + " HTTP/1.1\r\nHost: " + host_for_header + ":" + std::to_string(port_) +
                        "\r\nContent-Type: application/json\r\nContent-Length: " + std::to_string(body.size()) +
                        "\r\nConnection: keep-alive\r\n\r\n";
     for (int attempt = 0; attempt < 2; ++attempt) {

@@ -87,24 +87,80 @@ DnsConfig DnsConfig::load_system() {
     return cfg;
 }
 
-bool hosts_file_lookup(const std::string& path, const std::string& host, uint32_t* ipv4) {
+IpAddress IpAddress::v4(uint32_t network_order) {
+    IpAddress a;
+    a.family = AF_INET;
+    std::memcpy(a.bytes, &network_order, 4);
+    return a;
+}
+
+IpAddress IpAddress::parse(const std::string& text) {
+    IpAddress a;
+    if (inet_pton(AF_INET, text.c_str(), a.bytes) == 1) {
+        a.family = AF_INET;
+    } else if (inet_pton(AF_INET6, text.c_str(), a.bytes) == 1) {
+        a.family = AF_INET6;
+    }
+    return a;
+}
+
+std::string IpAddress::to_string() const {
+    char buf[INET6_ADDRSTRLEN] = "";
+    if (family == AF_INET || family == AF_INET6) inet_ntop(family, bytes, buf, sizeof buf);
+    return buf;
+}
+
+uint32_t IpAddress::v4_network_order() const {
+    uint32_t v = 0;
+    if (family == AF_INET) std::memcpy(&v, bytes, 4);
+    return v;
+}
+
+socklen_t IpAddress::to_sockaddr(uint16_t port, sockaddr_storage* out) const {
+    std::memset(out, 0, sizeof *out);
+    if (family == AF_INET6) {
+        auto* a = reinterpret_cast<sockaddr_in6*>(out);
+        a->sin6_family = AF_INET6;
+        a->sin6_port = htons(port);
+        std::memcpy(&a->sin6_addr, bytes, 16);
+        return sizeof *a;
+    }
+    auto* a = reinterpret_cast<sockaddr_in*>(out);
+    a->sin_family = AF_INET;
+    a->sin_port = htons(port);
+    std::memcpy(&a->sin_addr, bytes, 4);
+    return sizeof *a;
+}
+
+bool IpAddress::operator==(const IpAddress& o) const {
+    return family == o.family && std::memcmp(bytes, o.bytes, family == AF_INET6 ? 16 : 4) == 0;
+}
+
+bool hosts_file_lookup(const std::string& path, const std::string& host, IpAddress* out) {
     const std::string text = read_file(path);
     const std::string want = lower(host);
     std::istringstream is(text);
     std::string line;
+    IpAddress v6_match;
     while (std::getline(is, line)) {
         const size_t hash = line.find('#');
         if (hash != std::string::npos) line.erase(hash);
         const std::vector<std::string> tok = split_ws(line);
         if (tok.size() < 2) continue;
-        in_addr addr;
-        if (inet_pton(AF_INET, tok[0].c_str(), &addr) != 1) continue;  // IPv6 lines are skipped
+        const IpAddress addr = IpAddress::parse(tok[0]);
+        if (addr.family == 0) continue;
         for (size_t i = 1; i < tok.size(); ++i) {
-            if (lower(tok[i]) == want) {
-                *ipv4 = addr.s_addr;
+            if (lower(tok[i]) != want) continue;
+            if (addr.family == AF_INET) {
+                *out = addr;
                 return true;
             }
+            if (v6_match.family == 0) v6_match = addr;
         }
+    }
+    if (v6_match.family != 0) {
+        *out = v6_match;
+        return true;
     }
     return false;
 }
@@ -127,7 +183,7 @@ std::vector<std::string> dns_candidates(const std::string& host, const DnsConfig
     return out;
 }
 
-bool dns_build_query(const std::string& name, uint16_t id, std::vector<uint8_t>* out) {
+bool dns_build_query(const std::string& name, uint16_t id, std::vector<uint8_t>* out, uint16_t qtype) {
     out->clear();
     out->reserve(name.size() + 18);
     auto put16 = [&](uint16_t v) {
@@ -153,7 +209,7 @@ bool dns_build_query(const std::string& name, uint16_t id, std::vector<uint8_t>*
     }
     if (out->size() - 12 > 254) return false;
     out->push_back(0);
-    put16(1);  // QTYPE A
+    put16(qtype);
     put16(1);  // QCLASS IN
     return true;
 }
@@ -199,7 +255,7 @@ bool read_name(const uint8_t* d, size_t len, size_t pos, std::string* out) {
 
 }  // namespace
 
-DnsStatus dns_parse_response(const uint8_t* d, size_t len, uint16_t id, uint32_t* ipv4, bool* truncated) {
+DnsStatus dns_parse_response(const uint8_t* d, size_t len, uint16_t id, IpAddress* out, bool* truncated, uint16_t qtype) {
     if (truncated) *truncated = false;
     if (len < 12) return DnsStatus::kError;
     if (static_cast<uint16_t>((d[0] << 8) | d[1]) != id) return DnsStatus::kError;
@@ -235,8 +291,9 @@ DnsStatus dns_parse_response(const uint8_t* d, size_t len, uint16_t id, uint32_t
             p += 10;
             if (p + rdlen > len) return DnsStatus::kError;
             if (klass == 1 && owner == target) {
-                if (type == 1 && rdlen == 4) {
-                    std::memcpy(ipv4, d + p, 4);
+                if (type == qtype && ((qtype == kDnsTypeA && rdlen == 4) || (qtype == kDnsTypeAAAA && rdlen == 16))) {
+                    out->family = qtype == kDnsTypeA ? AF_INET : AF_INET6;
+                    std::memcpy(out->bytes, d + p, rdlen);
                     return DnsStatus::kOk;
                 }
                 if (type == 5) {
@@ -248,7 +305,7 @@ DnsStatus dns_parse_response(const uint8_t* d, size_t len, uint16_t id, uint32_t
             p += rdlen;
         }
     }
-    return DnsStatus::kNotFound;  // NODATA: the name exists but has no A record
+    return DnsStatus::kNoData;  // the name exists but has no record of this type
 }
 
 namespace {
@@ -289,8 +346,8 @@ int remaining_ms(int64_t deadline_ns, int cap_ms) {
 
 // One query/response exchange over UDP (or TCP when `tcp`). Returns kTimeout when nothing usable
 // arrived in time.
-DnsStatus exchange(const ServerAddr& server, const std::vector<uint8_t>& query, uint16_t id, bool tcp, int timeout_ms,
-                   uint32_t* ipv4, bool* truncated) {
+DnsStatus exchange(const ServerAddr& server, const std::vector<uint8_t>& query, uint16_t id, uint16_t qtype, bool tcp,
+                   int timeout_ms, IpAddress* out, bool* truncated) {
     const int fd = socket(server.family, (tcp ? SOCK_STREAM : SOCK_DGRAM) | SOCK_CLOEXEC | SOCK_NONBLOCK, 0);
     if (fd < 0) return DnsStatus::kError;
     DnsStatus result = DnsStatus::kTimeout;
@@ -335,7 +392,7 @@ DnsStatus exchange(const ServerAddr& server, const std::vector<uint8_t>& query, 
                 break;
             }
             if (!tcp) {
-                const DnsStatus st = dns_parse_response(buf, static_cast<size_t>(n), id, ipv4, truncated);
+                const DnsStatus st = dns_parse_response(buf, static_cast<size_t>(n), id, out, truncated, qtype);
                 if (st == DnsStatus::kError && static_cast<size_t>(n) >= 2 &&
                     static_cast<uint16_t>((buf[0] << 8) | buf[1]) != id) {
                     continue;  // a stray datagram for some other query: keep waiting
@@ -351,7 +408,7 @@ DnsStatus exchange(const ServerAddr& server, const std::vector<uint8_t>& query, 
                 break;
             }
             if (have < msg_len + 2) continue;
-            result = dns_parse_response(buf + 2, msg_len, id, ipv4, nullptr);
+            result = dns_parse_response(buf + 2, msg_len, id, out, nullptr, qtype);
             break;
         }
     } while (false);
@@ -361,17 +418,17 @@ DnsStatus exchange(const ServerAddr& server, const std::vector<uint8_t>& query, 
 
 }  // namespace
 
-DnsStatus resolve_ipv4(const std::string& host, const DnsConfig& cfg, uint32_t* ipv4, int deadline_ms) {
-    in_addr literal;
-    if (inet_pton(AF_INET, host.c_str(), &literal) == 1) {
-        *ipv4 = literal.s_addr;
+DnsStatus resolve_address(const std::string& host, const DnsConfig& cfg, IpAddress* out, int deadline_ms) {
+    const IpAddress literal = IpAddress::parse(host);
+    if (literal.family != 0) {
+        *out = literal;
         return DnsStatus::kOk;
     }
     if (ascii_iequals(host, "localhost")) {
-        *ipv4 = htonl(INADDR_LOOPBACK);
+        *out = IpAddress::v4(htonl(INADDR_LOOPBACK));
         return DnsStatus::kOk;
     }
-    if (hosts_file_lookup(cfg.hosts_file, host, ipv4)) return DnsStatus::kOk;
+    if (hosts_file_lookup(cfg.hosts_file, host, out)) return DnsStatus::kOk;
 
     const int64_t deadline_ns = deadline_ms > 0 ? monotonic_ns() + static_cast<int64_t>(deadline_ms) * 1000000 : 0;
     std::vector<ServerAddr> servers;
@@ -384,30 +441,39 @@ DnsStatus resolve_ipv4(const std::string& host, const DnsConfig& cfg, uint32_t* 
     bool any_timeout = false;
     bool any_error = false;
     for (const std::string& name : dns_candidates(host, cfg)) {
-        uint16_t id = 0;
-        if (getrandom(&id, sizeof id, GRND_NONBLOCK) != static_cast<ssize_t>(sizeof id))
-            id = static_cast<uint16_t>(monotonic_ns() & 0xFFFF);
-        std::vector<uint8_t> query;
-        if (!dns_build_query(name, id, &query)) continue;
-        bool answered = false;
-        for (int attempt = 0; attempt < cfg.attempts && !answered; ++attempt) {
-            for (const ServerAddr& server : servers) {
-                const int timeout_ms = remaining_ms(deadline_ns, cfg.timeout_ms);
-                if (timeout_ms <= 0) return DnsStatus::kTimeout;
-                bool truncated = false;
-                DnsStatus st = exchange(server, query, id, false, timeout_ms, ipv4, &truncated);
-                if (truncated && st != DnsStatus::kOk) {
-                    const int t2 = remaining_ms(deadline_ns, cfg.timeout_ms);
-                    if (t2 > 0) st = exchange(server, query, id, true, t2, ipv4, nullptr);
+        // IPv4 first; a name that exists only as AAAA (an IPv6-only cluster) is found by the
+        // second question.
+        for (const uint16_t qtype : {kDnsTypeA, kDnsTypeAAAA}) {
+            uint16_t id = 0;
+            if (getrandom(&id, sizeof id, GRND_NONBLOCK) != static_cast<ssize_t>(sizeof id))
+                id = static_cast<uint16_t>(monotonic_ns() & 0xFFFF);
+            std::vector<uint8_t> query;
+            if (!dns_build_query(name, id, &query, qtype)) break;
+            bool answered = false;  // some server said "no such name" or "no such record"
+            bool try_other_family = false;
+            for (int attempt = 0; attempt < cfg.attempts && !answered; ++attempt) {
+                for (const ServerAddr& server : servers) {
+                    const int timeout_ms = remaining_ms(deadline_ns, cfg.timeout_ms);
+                    if (timeout_ms <= 0) return DnsStatus::kTimeout;
+                    bool truncated = false;
+                    DnsStatus st = exchange(server, query, id, qtype, false, timeout_ms, out, &truncated);
+                    if (truncated && st != DnsStatus::kOk) {
+                        const int t2 = remaining_ms(deadline_ns, cfg.timeout_ms);
+                        if (t2 > 0) st = exchange(server, query, id, qtype, true, t2, out, nullptr);
+                    }
+                    if (st == DnsStatus::kOk) return DnsStatus::kOk;
+                    if (st == DnsStatus::kNotFound || st == DnsStatus::kNoData) {
+                        answered = true;  // authoritative "no"
+                        try_other_family = st == DnsStatus::kNoData;
+                        break;
+                    }
+                    if (st == DnsStatus::kTimeout) any_timeout = true;
+                    if (st == DnsStatus::kError) any_error = true;
                 }
-                if (st == DnsStatus::kOk) return DnsStatus::kOk;
-                if (st == DnsStatus::kNotFound) {
-                    answered = true;  // authoritative "no": move on to the next candidate name
-                    break;
-                }
-                if (st == DnsStatus::kTimeout) any_timeout = true;
-                if (st == DnsStatus::kError) any_error = true;
             }
+            // NXDOMAIN covers every record type, and silence will not turn into an answer by
+            // asking for AAAA: in both cases go on to the next candidate name.
+            if (!try_other_family) break;
         }
     }
     if (any_timeout) return DnsStatus::kTimeout;

@@ -1,5 +1,5 @@
-// A small stub resolver: /etc/hosts, then A-record queries to the name servers of
-// /etc/resolv.conf with search-list and ndots handling.
+// A small stub resolver: /etc/hosts, then A (and, failing that, AAAA) queries to the name servers
+// of /etc/resolv.conf with search-list and ndots handling.
 //
 // Why not getaddrinfo(): the service is shipped as one fully static executable in a FROM-scratch
 // image (the analogue of the reference's self-contained uber-jar, /root/reference/pom.xml:230-241,
@@ -14,11 +14,28 @@
 // loops never call it.
 #pragma once
 
+#include <sys/socket.h>
+
 #include <cstdint>
 #include <string>
 #include <vector>
 
 namespace hola {
+
+// An IPv4 or IPv6 address in network byte order.
+struct IpAddress {
+    int family = 0;  // AF_INET, AF_INET6, or 0 for "none"
+    uint8_t bytes[16] = {0};
+
+    static IpAddress v4(uint32_t network_order);
+    // Parses a textual address ("10.1.2.3", "fd00::1"). family stays 0 when it is neither.
+    static IpAddress parse(const std::string& text);
+    std::string to_string() const;
+    uint32_t v4_network_order() const;
+    // Fills `out` for connect()/bind(); returns the length to pass along.
+    socklen_t to_sockaddr(uint16_t port, sockaddr_storage* out) const;
+    bool operator==(const IpAddress& o) const;
+};
 
 struct DnsConfig {
     std::vector<std::string> nameservers;  // textual IPv4/IPv6 addresses
@@ -36,22 +53,28 @@ struct DnsConfig {
     static DnsConfig load_system();
 };
 
-enum class DnsStatus { kOk, kNotFound, kTimeout, kError };
+// kNotFound: the name does not exist (NXDOMAIN). kNoData: it exists but has no record of the
+// type asked for (worth asking again for the other address family).
+enum class DnsStatus { kOk, kNotFound, kNoData, kTimeout, kError };
 
-// Looks `host` up in the hosts file. Returns true and the address (network byte order).
-bool hosts_file_lookup(const std::string& path, const std::string& host, uint32_t* ipv4);
+constexpr uint16_t kDnsTypeA = 1;
+constexpr uint16_t kDnsTypeAAAA = 28;
+
+// Looks `host` up in the hosts file; IPv4 entries win over IPv6 ones.
+bool hosts_file_lookup(const std::string& path, const std::string& host, IpAddress* out);
 
 // The candidate fully-qualified names for `host`, in the order a stub resolver tries them.
 std::vector<std::string> dns_candidates(const std::string& host, const DnsConfig& cfg);
 
 // Wire format helpers (exposed for unit tests).
-bool dns_build_query(const std::string& name, uint16_t id, std::vector<uint8_t>* out);
-// Parses a response to query `id` for `name`. kOk sets *ipv4 (network order) to the first A
-// record, following CNAMEs inside the message. *truncated is set when the TC bit is on.
-DnsStatus dns_parse_response(const uint8_t* data, size_t len, uint16_t id, uint32_t* ipv4, bool* truncated);
+bool dns_build_query(const std::string& name, uint16_t id, std::vector<uint8_t>* out, uint16_t qtype = kDnsTypeA);
+// Parses a response to query `id`. kOk sets *out to the first record of type `qtype` for the
+// queried name, following CNAMEs inside the message. *truncated is set when the TC bit is on.
+DnsStatus dns_parse_response(const uint8_t* data, size_t len, uint16_t id, IpAddress* out, bool* truncated,
+                             uint16_t qtype = kDnsTypeA);
 
-// Full blocking lookup: literal, "localhost", hosts file, then DNS. `deadline_ms` bounds the
-// whole operation (0: only the per-try timeouts apply).
-DnsStatus resolve_ipv4(const std::string& host, const DnsConfig& cfg, uint32_t* ipv4, int deadline_ms = 0);
+// Full blocking lookup: literal, "localhost", hosts file, then DNS (A first; AAAA when the name
+// has no A record). `deadline_ms` bounds the whole operation (0: only the per-try timeouts apply).
+DnsStatus resolve_address(const std::string& host, const DnsConfig& cfg, IpAddress* out, int deadline_ms = 0);
 
 }  // namespace hola

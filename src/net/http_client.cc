@@ -301,28 +301,26 @@ void HttpClient::dispatch(const std::shared_ptr<Pending>& p) {
         }
     }
     std::shared_ptr<bool> alive = alive_;
-    resolver_->resolve(p->host, loop_, [this, alive, p](bool ok, uint32_t ipv4) {
+    resolver_->resolve(p->host, loop_, [this, alive, p](bool ok, const IpAddress& address) {
         if (!*alive || p->cancelled) return;
         if (!ok) {
             fail(p, ClientResult::Code::kResolveFailed);
             return;
         }
-        start_connect(p, ipv4);
+        start_connect(p, address);
     });
 }
 
-void HttpClient::start_connect(const std::shared_ptr<Pending>& p, uint32_t ipv4) {
-    const int fd = socket(AF_INET, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
+void HttpClient::start_connect(const std::shared_ptr<Pending>& p, const IpAddress& address) {
+    const int fd = socket(address.family == AF_INET6 ? AF_INET6 : AF_INET, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
     if (fd < 0) {
         fail(p, ClientResult::Code::kConnectFailed);
         return;
     }
     set_nodelay(fd);
-    sockaddr_in addr{};
-    addr.sin_family = AF_INET;
-    addr.sin_port = htons(p->port);
-    addr.sin_addr.s_addr = ipv4;
-    const int rc = connect(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr);
+    sockaddr_storage addr;
+    const socklen_t addr_len = address.to_sockaddr(p->port, &addr);
+    const int rc = connect(fd, reinterpret_cast<sockaddr*>(&addr), addr_len);
     if (rc != 0 && errno != EINPROGRESS) {
         close(fd);
         fail(p, ClientResult::Code::kConnectFailed);

@@ -63,7 +63,7 @@ class HttpClient {
     struct Pending;
 
     void dispatch(const std::shared_ptr<Pending>& p);
-    void start_connect(const std::shared_ptr<Pending>& p, uint32_t ipv4);
+    void start_connect(const std::shared_ptr<Pending>& p, const IpAddress& address);
     void fail(const std::shared_ptr<Pending>& p, ClientResult::Code code);
     void finish(Conn* conn, ClientResult&& result, bool reusable);
     void retry_or_fail(Conn* conn, ClientResult::Code code);

@@ -29,23 +29,23 @@ void Resolver::shutdown() {
     state_->cv.notify_all();
 }
 
-void Resolver::set_static(const std::string& host, uint32_t ipv4) {
+void Resolver::set_static(const std::string& host, const IpAddress& address) {
     std::lock_guard<std::mutex> lock(state_->mu);
     Entry e;
     e.ok = true;
-    e.ipv4 = ipv4;
+    e.address = address;
     e.permanent = true;
     state_->cache[host] = e;
 }
 
 void Resolver::resolve(const std::string& host, EventLoop* loop, Callback cb) {
-    in_addr literal;
-    if (inet_pton(AF_INET, host.c_str(), &literal) == 1) {
-        cb(true, literal.s_addr);
+    const IpAddress literal = IpAddress::parse(host);
+    if (literal.family != 0) {
+        cb(true, literal);
         return;
     }
     if (host == "localhost") {
-        cb(true, htonl(INADDR_LOOPBACK));
+        cb(true, IpAddress::v4(htonl(INADDR_LOOPBACK)));
         return;
     }
     const int64_t now = monotonic_ns();
@@ -55,7 +55,7 @@ void Resolver::resolve(const std::string& host, EventLoop* loop, Callback cb) {
         if (it != state_->cache.end() && (it->second.permanent || it->second.expires_ns > now)) {
             const Entry e = it->second;
             lock.unlock();
-            cb(e.ok, e.ipv4);
+            cb(e.ok, e.address);
             return;
         }
         auto& waiters = state_->inflight[host];
@@ -81,7 +81,7 @@ void Resolver::thread_main(std::shared_ptr<State> st) {
         // The system configuration is re-read per lookup (it is tiny, lookups are rare, and a
         // pod's resolv.conf can be rewritten under a running process).
         Entry e;
-        e.ok = resolve_ipv4(host, DnsConfig::load_system(), &e.ipv4) == DnsStatus::kOk;
+        e.ok = resolve_address(host, DnsConfig::load_system(), &e.address) == DnsStatus::kOk;
         e.expires_ns = monotonic_ns() + (e.ok ? st->positive_ttl_ns : st->negative_ttl_ns);
         // Answers are posted under the lock so that shutdown() (which takes it) cannot return
         // while a post to a soon-to-be-destroyed loop is still in progress.
@@ -95,8 +95,8 @@ void Resolver::thread_main(std::shared_ptr<State> st) {
         st->inflight.erase(it);
         for (auto& w : waiters) {
             const bool ok = e.ok;
-            const uint32_t ip = e.ipv4;
-            w.loop->post([cb = std::move(w.cb), ok, ip] { cb(ok, ip); });
+            const IpAddress address = e.address;
+            w.loop->post([cb = std::move(w.cb), ok, address] { cb(ok, address); });
         }
     }
 }

@@ -7,7 +7,7 @@
 // asking loop; the caller's own timer provides the cut-off. Results are cached the way the JVM
 // caches them: 30 s for a success, 10 s for a failure.
 //
-// Numeric IPv4 literals and "localhost" are answered inline without touching the helper thread.
+// Numeric IPv4/IPv6 literals and "localhost" are answered inline without touching the helper thread.
 #pragma once
 
 #include <condition_variable>
@@ -21,14 +21,15 @@
 #include <unordered_map>
 #include <vector>
 
+#include "net/dns.h"
 #include "net/event_loop.h"
 
 namespace hola {
 
 class Resolver {
  public:
-    // ok=false means the name did not resolve; ipv4 is in network byte order.
-    using Callback = std::function<void(bool ok, uint32_t ipv4)>;
+    // ok=false means the name did not resolve.
+    using Callback = std::function<void(bool ok, const IpAddress& address)>;
 
     explicit Resolver(int threads = 2, int positive_ttl_s = 30, int negative_ttl_s = 10);
     ~Resolver();
@@ -39,13 +40,13 @@ class Resolver {
     // or literal, otherwise later via loop->post(). Must be called on `loop`'s thread.
     void resolve(const std::string& host, EventLoop* loop, Callback cb);
 
-    // Test hook: pins a name to an address (network byte order), bypassing the system resolver.
-    void set_static(const std::string& host, uint32_t ipv4);
+    // Pins a name to an address, bypassing hosts file and DNS (--resolve NAME=ADDR).
+    void set_static(const std::string& host, const IpAddress& address);
 
  private:
     struct Entry {
         bool ok = false;
-        uint32_t ipv4 = 0;
+        IpAddress address;
         int64_t expires_ns = 0;
         bool permanent = false;
     };

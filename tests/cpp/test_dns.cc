@@ -92,29 +92,31 @@ TEST(dns_query_wire_format) {
     CHECK(!dns_build_query("bad..name", 1, &q));
     CHECK(!dns_build_query(std::string(64, 'x') + ".com", 1, &q));
     CHECK(!dns_build_query(".", 1, &q));
+    CHECK(dns_build_query("a.b", 1, &q, kDnsTypeAAAA));
+    CHECK_EQ(static_cast<int>(q[q.size() - 3]), 28);  // QTYPE AAAA
 }
 
 TEST(dns_response_parsing) {
-    uint32_t ip = 0;
+    IpAddress ip;
     bool tc = false;
     // Plain A answer with a compressed owner name.
     auto r = response(7, "aloha.test", 0, {record(kPointerToQuestion, 1, {10, 1, 2, 3})});
     CHECK(dns_parse_response(r.data(), r.size(), 7, &ip, &tc) == DnsStatus::kOk);
-    CHECK_EQ(ntohl(ip), uint32_t{0x0A010203});
+    CHECK_EQ(ntohl(ip.v4_network_order()), uint32_t{0x0A010203});
     CHECK(!tc);
     // CNAME chain: aloha.test -> real.test -> 192.0.2.9, owner names spelled out and upper-cased.
     r = response(8, "aloha.test", 0,
                  {record(kPointerToQuestion, 5, encode_name("REAL.test")), record(encode_name("real.TEST"), 1, {192, 0, 2, 9})});
     CHECK(dns_parse_response(r.data(), r.size(), 8, &ip, nullptr) == DnsStatus::kOk);
-    CHECK_EQ(ntohl(ip), uint32_t{0xC0000209});
+    CHECK_EQ(ntohl(ip.v4_network_order()), uint32_t{0xC0000209});
     // A record listed before the alias that leads to it.
     r = response(8, "aloha.test", 0,
                  {record(encode_name("real.test"), 1, {192, 0, 2, 10}), record(kPointerToQuestion, 5, encode_name("real.test"))});
     CHECK(dns_parse_response(r.data(), r.size(), 8, &ip, nullptr) == DnsStatus::kOk);
-    CHECK_EQ(ntohl(ip), uint32_t{0xC000020A});
+    CHECK_EQ(ntohl(ip.v4_network_order()), uint32_t{0xC000020A});
     // An A record for some other name does not count.
     r = response(9, "aloha.test", 0, {record(encode_name("other.test"), 1, {1, 1, 1, 1})});
-    CHECK(dns_parse_response(r.data(), r.size(), 9, &ip, nullptr) == DnsStatus::kNotFound);
+    CHECK(dns_parse_response(r.data(), r.size(), 9, &ip, nullptr) == DnsStatus::kNoData);
     // NXDOMAIN, SERVFAIL, wrong id, truncation, AAAA only, garbage.
     r = response(10, "aloha.test", 3, {});
     CHECK(dns_parse_response(r.data(), r.size(), 10, &ip, nullptr) == DnsStatus::kNotFound);
@@ -122,10 +124,15 @@ TEST(dns_response_parsing) {
     CHECK(dns_parse_response(r.data(), r.size(), 10, &ip, nullptr) == DnsStatus::kError);
     CHECK(dns_parse_response(r.data(), r.size(), 11, &ip, nullptr) == DnsStatus::kError);
     r = response(12, "aloha.test", 0, {}, true);
-    CHECK(dns_parse_response(r.data(), r.size(), 12, &ip, &tc) == DnsStatus::kNotFound);
+    CHECK(dns_parse_response(r.data(), r.size(), 12, &ip, &tc) == DnsStatus::kNoData);
     CHECK(tc);
-    r = response(13, "aloha.test", 0, {record(kPointerToQuestion, 28, std::vector<uint8_t>(16, 0))});
-    CHECK(dns_parse_response(r.data(), r.size(), 13, &ip, nullptr) == DnsStatus::kNotFound);
+    std::vector<uint8_t> v6(16, 0);
+    v6[0] = 0xfd;
+    v6[15] = 0x01;
+    r = response(13, "aloha.test", 0, {record(kPointerToQuestion, 28, v6)});
+    CHECK(dns_parse_response(r.data(), r.size(), 13, &ip, nullptr) == DnsStatus::kNoData);  // asked for A, got AAAA only
+    CHECK(dns_parse_response(r.data(), r.size(), 13, &ip, nullptr, kDnsTypeAAAA) == DnsStatus::kOk);
+    CHECK_EQ(ip.to_string(), std::string("fd00::1"));
     const uint8_t junk[] = {0, 13, 0x81, 0x80, 0, 1, 0, 5, 0, 0, 0, 0, 0xC0};
     CHECK(dns_parse_response(junk, sizeof junk, 13, &ip, nullptr) == DnsStatus::kError);
     // Every truncation of a valid message is handled without reading out of bounds.
@@ -146,20 +153,23 @@ TEST(dns_hosts_file_and_literals) {
     const std::string text = "127.0.0.1 localhost\n::1 ip6-localhost\n# comment\n10.9.8.7   Aloha aloha.internal # trailing\n";
     CHECK(write(fd, text.data(), text.size()) == static_cast<ssize_t>(text.size()));
     close(fd);
-    uint32_t ip = 0;
+    IpAddress ip;
     CHECK(hosts_file_lookup(tmpl, "aloha", &ip));
-    CHECK_EQ(ntohl(ip), uint32_t{0x0A090807});
+    CHECK_EQ(ntohl(ip.v4_network_order()), uint32_t{0x0A090807});
     CHECK(hosts_file_lookup(tmpl, "ALOHA.internal", &ip));
     CHECK(!hosts_file_lookup(tmpl, "trailing", &ip));
-    CHECK(!hosts_file_lookup(tmpl, "ip6-localhost", &ip));
+    CHECK(hosts_file_lookup(tmpl, "ip6-localhost", &ip));  // IPv6-only entries are usable too
+    CHECK_EQ(ip.to_string(), std::string("::1"));
     CHECK(!hosts_file_lookup("/nonexistent/hosts", "aloha", &ip));
     DnsConfig cfg = DnsConfig::parse("nameserver 127.0.0.1\noptions timeout:1 attempts:1\n");
     cfg.hosts_file = tmpl;
-    CHECK(resolve_ipv4("192.0.2.55", cfg, &ip) == DnsStatus::kOk);
-    CHECK_EQ(ntohl(ip), uint32_t{0xC0000237});
-    CHECK(resolve_ipv4("LocalHost", cfg, &ip) == DnsStatus::kOk);
-    CHECK_EQ(ntohl(ip), uint32_t{0x7F000001});
-    CHECK(resolve_ipv4("aloha", cfg, &ip) == DnsStatus::kOk);
-    CHECK_EQ(ntohl(ip), uint32_t{0x0A090807});
+    CHECK(resolve_address("192.0.2.55", cfg, &ip) == DnsStatus::kOk);
+    CHECK_EQ(ntohl(ip.v4_network_order()), uint32_t{0xC0000237});
+    CHECK(resolve_address("fd00::42", cfg, &ip) == DnsStatus::kOk);
+    CHECK(ip.family == AF_INET6);
+    CHECK(resolve_address("LocalHost", cfg, &ip) == DnsStatus::kOk);
+    CHECK_EQ(ntohl(ip.v4_network_order()), uint32_t{0x7F000001});
+    CHECK(resolve_address("aloha", cfg, &ip) == DnsStatus::kOk);
+    CHECK_EQ(ntohl(ip.v4_network_order()), uint32_t{0x0A090807});
     unlink(tmpl);
 }

@@ -61,12 +61,18 @@ class FakeDns:
             pos += 1 + n
         name = ".".join(labels).lower()
         question = data[12:pos + 5]
+        (qtype,) = struct.unpack(">H", data[pos + 1:pos + 3])
         ip = self.records.get(name)
         if truncated:
             return name, qid + b"\x83\x80" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
         if ip is None:
             return name, qid + b"\x81\x83" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
-        answer = b"\xc0\x0c" + struct.pack(">HHIH", 1, 1, 30, 4) + socket.inet_aton(ip)
+        is_v6 = ":" in ip
+        if (qtype == 1 and is_v6) or (qtype == 28 and not is_v6) or qtype not in (1, 28):
+            # The name exists but has no record of the requested type: NOERROR, zero answers.
+            return name, qid + b"\x81\x80" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
+        rdata = socket.inet_pton(socket.AF_INET6, ip) if is_v6 else socket.inet_aton(ip)
+        answer = b"\xc0\x0c" + struct.pack(">HHIH", qtype, 1, 30, len(rdata)) + rdata
         return name, qid + b"\x81\x80" + b"\x00\x01\x00\x01\x00\x00\x00\x00" + question + answer
 
     def _serve(self):
@@ -232,3 +238,64 @@ def test_second_name_server_is_tried_when_the_first_is_dead(hola_server, fake_al
     srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port,
                             "-Dhystrix.command.default.execution.isolation.thread.timeoutInMilliseconds=3000"], env=env)
     assert chain(srv)[1:] == fake_aloha.payload
+
+
+class _V6Aloha:
+    """A downstream that exists only on IPv6 (an IPv6-only cluster)."""
+
+    def __init__(self, payload):
+        from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
+        seen = self.seen = []
+
+        class Handler(BaseHTTPRequestHandler):
+            protocol_version = "HTTP/1.1"
+
+            def log_message(self, *a):
+                pass
+
+            def do_GET(self):
+                seen.append(self.headers.get("Host"))
+                body = json.dumps(payload).encode()
+                self.send_response(200)
+                self.send_header("Content-Type", "application/json")
+                self.send_header("Content-Length", str(len(body)))
+                self.end_headers()
+                self.wfile.write(body)
+
+        class Server(ThreadingHTTPServer):
+            address_family = socket.AF_INET6
+            daemon_threads = True
+
+        self.httpd = Server(("::1", 0), Handler)
+        self.port = self.httpd.server_address[1]
+        threading.Thread(target=self.httpd.serve_forever, daemon=True).start()
+
+    def stop(self):
+        self.httpd.shutdown()
+        self.httpd.server_close()
+
+
+@pytest.fixture
+def v6_aloha():
+    try:
+        srv = _V6Aloha(["Aloha over IPv6"])
+    except OSError:
+        pytest.skip("no IPv6 loopback on this machine")
+    yield srv
+    srv.stop()
+
+
+def test_ipv6_only_downstream_via_aaaa(hola_server, v6_aloha, fake_dns, tmp_path):
+    """The name has no A record, only AAAA: the second question finds it."""
+    dns = fake_dns({"aloha.msa.svc.cluster.local": "::1"})
+    srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % v6_aloha.port], env=dns_env(tmp_path, dns))
+    assert chain(srv) == ["Hola de unknown", "Aloha over IPv6"]
+    assert dns.queries[:2] == ["aloha.msa.svc.cluster.local", "aloha.msa.svc.cluster.local"]  # A, then AAAA
+
+
+def test_ipv6_literal_and_pinned_downstream(hola_server, v6_aloha):
+    srv = hola_server(args=["--aloha-url", "http://[::1]:%d/" % v6_aloha.port])
+    assert chain(srv) == ["Hola de unknown", "Aloha over IPv6"]
+    assert v6_aloha.seen[-1] == "[::1]:%d" % v6_aloha.port  # literal goes into the Host header in brackets
+    srv2 = hola_server(args=["--aloha-url", "http://aloha:%d/" % v6_aloha.port, "--resolve", "aloha=::1"])
+    assert chain(srv2) == ["Hola de unknown", "Aloha over IPv6"]
