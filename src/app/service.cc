@@ -29,7 +29,7 @@ std::string usage_text() {
            "  --conf FILE                 same as -Dconf=FILE\n"
            "  --port N, --bind ADDR       same as the swarm.* definitions (port 0: pick a free one; --bind :: listens\n"
            "                              on IPv6 and IPv4)\n"
-           "  --threads N                 event-loop threads (default: one per available CPU)\n"
+           "  --threads N                 event-loop threads (default: one per available CPU, capped by the cgroup CPU quota)\n"
            "  --cpus LIST                 pin thread i to the i-th CPU of LIST (e.g. 0,1,2,3 or 0-3)\n"
            "  --accept-mode MODE          reuseport (default; one listener per thread) | rr (one acceptor, round-robin)\n"
            "  --aloha-url URL             downstream base URL (default http://aloha:8080/)\n"

@@ -11,6 +11,7 @@
 
 #include <cerrno>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace hola {
@@ -500,14 +501,43 @@ Server::Server(ServerOptions options, Application* app) : options_(std::move(opt
 
 Server::~Server() { stop(); }
 
+namespace {
+
+// How many event-loop threads make sense by default: the CPUs this process may run on, capped by
+// the container's CPU quota (cgroup v2 cpu.max, or the v1 cfs files). A pod limited to one CPU on
+// a 64-core node should get one loop, not 64 taking turns.
+int default_thread_count() {
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    int n = sched_getaffinity(0, sizeof set, &set) == 0 ? CPU_COUNT(&set) : 1;
+    if (n <= 0) n = 1;
+    long quota = -1, period = -1;
+    if (FILE* f = std::fopen("/sys/fs/cgroup/cpu.max", "r")) {
+        char q[32] = "";
+        if (std::fscanf(f, "%31s %ld", q, &period) == 2 && std::strcmp(q, "max") != 0) quota = std::atol(q);
+        std::fclose(f);
+    } else {
+        if (FILE* fq = std::fopen("/sys/fs/cgroup/cpu/cpu.cfs_quota_us", "r")) {
+            if (std::fscanf(fq, "%ld", &quota) != 1) quota = -1;
+            std::fclose(fq);
+        }
+        if (FILE* fp = std::fopen("/sys/fs/cgroup/cpu/cpu.cfs_period_us", "r")) {
+            if (std::fscanf(fp, "%ld", &period) != 1) period = -1;
+            std::fclose(fp);
+        }
+    }
+    if (quota > 0 && period > 0) {
+        const int by_quota = static_cast<int>((quota + period - 1) / period);
+        if (by_quota >= 1 && by_quota < n) n = by_quota;
+    }
+    return n;
+}
+
+}  // namespace
+
 bool Server::start(std::string* error) {
     int n = options_.threads;
-    if (n <= 0) {
-        cpu_set_t set;
-        CPU_ZERO(&set);
-        n = sched_getaffinity(0, sizeof set, &set) == 0 ? CPU_COUNT(&set) : 1;
-        if (n <= 0) n = 1;
-    }
+    if (n <= 0) n = default_thread_count();
     options_.threads = n;
     for (int i = 0; i < n; ++i) {
         workers_.emplace_back(new Worker(i, options_, app_));
