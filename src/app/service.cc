@@ -35,7 +35,7 @@ std::string usage_text() {
            "  --aloha-url URL             downstream base URL (default http://aloha:8080/)\n"
            "  --feign-max-attempts N      tries per downstream call on connection failures (default 5, as Feign's\n"
            "                              default Retryer: pauses of 150, 225, 337, 506 ms; 1 disables retrying)\n"
-           "  --resolve NAME=IPV4         answer lookups of NAME with IPV4 instead of asking the system resolver\n"
+           "  --resolve NAME=ADDRESS      answer lookups of NAME with that IPv4/IPv6 address instead of hosts file and DNS\n"
            "  --zipkin-url URL            overrides env ZIPKIN_SERVER_URL; unset/empty disables tracing\n"
            "  --zipkin-flush-ms N         span reporter period (default 1000)\n"
            "  --hystrix-config FILE       properties file with hystrix.* keys (default: the reference's config.properties values)\n"
