@@ -257,6 +257,103 @@ def test_breaker_invariants(steps):
     assert cmd["rollingCountShortCircuited"] == 0  # everything has aged out of the 10 s window
 
 
+class BreakerModel:
+    """Independent Python restatement of the breaker rules (Hystrix 1.5.1, reference settings):
+    500 ms health buckets over a 10 s window, only closed buckets visible; open at >= 5 requests
+    and >= 50 % errors; one trial per 5 s sleep window; success closes and wipes the window;
+    bulkhead of 10 concurrent executions, rejections count as errors."""
+
+    BUCKET, WINDOW, THRESHOLD, ERR_PCT, SLEEP, POOL = 500, 10000, 5, 50, 5000, 10
+
+    def __init__(self):
+        self.events = []  # (time, is_error) of everything that counts as a request
+        self.origin = None  # buckets are aligned to the first event
+        self.window_start = None  # after a reset, older events are forgotten
+        self.open = False
+        self.tested = 0
+        self.active = 0
+
+    def _visible(self, now):
+        if self.origin is None:
+            return []
+        current_bucket_start = self.origin + ((now - self.origin) // self.BUCKET) * self.BUCKET
+        oldest = current_bucket_start - self.WINDOW
+        lo = oldest if self.window_start is None else max(oldest, self.window_start)
+        return [e for (t, e) in self.events if lo <= t < current_bucket_start]
+
+    def _touch(self, now):
+        if self.origin is None:
+            self.origin = now
+
+    def is_open(self, now):
+        self._touch(now)
+        if self.open:
+            return True
+        seen = self._visible(now)
+        total, errors = len(seen), sum(seen)
+        if total < self.THRESHOLD or int(errors / total * 100) < self.ERR_PCT:
+            return False
+        self.open, self.tested = True, now
+        return True
+
+    def admit(self, now):
+        self._touch(now)
+        if self.is_open(now):
+            if now > self.tested + self.SLEEP:
+                self.tested = now
+            else:
+                return native.SHORT_CIRCUITED
+        if self.active >= self.POOL:
+            self.events.append((now, 1))
+            return native.POOL_REJECTED
+        self.active += 1
+        return native.RUN
+
+    def complete(self, now, outcome):
+        self._touch(now)
+        self.active -= 1
+        self.events.append((now, 0 if outcome == native.SUCCESS else 1))
+        if outcome == native.SUCCESS and self.open:
+            self.open = False
+            # The window restarts at `now`: bucket alignment moves with it.
+            self.origin = now
+            self.window_start = now
+            self.events = []
+
+
+@settings(max_examples=200, deadline=None)
+@given(st.lists(st.tuples(st.integers(min_value=0, max_value=1500),      # time step
+                          st.sampled_from(["call", "call", "call", "finish"]),
+                          st.sampled_from([native.SUCCESS, native.FAILURE, native.FAILURE, native.TIMEOUT]),
+                          st.integers(min_value=0, max_value=3)),        # hold the call open for this many later steps
+                min_size=1, max_size=80))
+def test_breaker_matches_independent_model(steps):
+    real, model = native.Breaker(), BreakerModel()
+    now = 10_000
+    in_flight = []  # (remaining_steps, outcome)
+    for dt, action, outcome, hold in steps:
+        now += dt
+        # Finish calls whose time has come (both sides see the same completions at the same time).
+        still = []
+        for remaining, out in in_flight:
+            if remaining <= 0 or action == "finish":
+                real.complete(now, out, 1)
+                model.complete(now, out)
+            else:
+                still.append((remaining - 1, out))
+        in_flight = still
+        if action == "call":
+            a, b = real.admit(now), model.admit(now)
+            assert a == b, (now, a, b)
+            if a == native.RUN:
+                if hold == 0:
+                    real.complete(now, outcome, 1)
+                    model.complete(now, outcome)
+                else:
+                    in_flight.append((hold, outcome))
+        assert real.is_open(now) == model.is_open(now), now
+
+
 def test_breaker_custom_config_text():
     b = native.Breaker("hystrix.command.default.circuitBreaker.requestVolumeThreshold=2\n"
                        "hystrix.command.default.execution.isolation.thread.timeoutInMilliseconds=250\n")
