@@ -65,8 +65,16 @@ class HolaServer:
         if not self._listening.wait(self.start_timeout):
             self.stop()
             raise RuntimeError("hola did not start: " + "".join(self.stderr_lines)[-2000:])
-        if self.proc.poll() is not None and self.port == 0:
-            raise RuntimeError("hola exited with %s: %s" % (self.proc.returncode, "".join(self.stderr_lines)[-2000:]))
+        if self.port == 0:
+            # stderr reached EOF without a "listening" line: the process is on its way out.
+            try:
+                self.proc.wait(5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+                self.proc.wait()
+            code = self.proc.returncode
+            self.proc = None
+            raise RuntimeError("hola exited with %s before listening: %s" % (code, "".join(self.stderr_lines)[-2000:]))
         self.startup_seconds = time.monotonic() - t0
         return self
 
