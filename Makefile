@@ -8,6 +8,8 @@
 #   make asan       AddressSanitizer + UBSan variant under build/asan/
 #   make tsan       ThreadSanitizer variant under build/tsan/
 #   make test       run the C++ unit tests
+#   make check      C++ tests + pytest + the black-box tests under ASan/UBSan and TSan
+#   make cov        gcov-instrumented variant under build/cov/ (see tools/coverage.sh)
 #   make clean
 
 CXX      ?= g++
@@ -38,7 +40,7 @@ TEST_OBJ := $(patsubst tests/cpp/%.cc,$(BUILD)/obj/tests/%.o,$(TEST_SRC))
 
 TARGETS := $(BUILD)/hola $(BUILD)/hola-load $(BUILD)/hola-coldstart $(BUILD)/libhola.so $(BUILD)/hola_tests
 
-.PHONY: all static asan tsan cov test clean
+.PHONY: all static asan tsan cov test check clean
 all: $(TARGETS)
 
 $(BUILD)/obj/%.o: src/%.cc
@@ -85,6 +87,15 @@ cov:
 
 test: $(BUILD)/hola_tests
 	$(BUILD)/hola_tests
+
+# Everything: C++ unit tests, the Python suite, then the black-box part again under both sanitizers.
+BLACKBOX := tests/test_contract.py tests/test_server_core.py tests/test_chaining.py tests/test_tracing.py \
+            tests/test_stream.py tests/test_dns.py tests/test_fuzz.py
+check: all
+	$(BUILD)/hola_tests
+	python -m pytest tests -q
+	python -m pytest $(BLACKBOX) -q --variant asan
+	python -m pytest $(BLACKBOX) -q --variant tsan
 
 clean:
 	rm -rf build
