@@ -16,7 +16,6 @@ import os
 import sys
 import threading
 import time
-from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
 from pathlib import Path
 from typing import Dict, List, Optional
 
@@ -103,159 +102,7 @@ def hola_server(request):
     assert not problems, "sanitizer findings:\n" + "\n----\n".join(problems)
 
 
-class _FakeServer(ThreadingHTTPServer):
-    # The default accept backlog of 5 drops simultaneous connects when the machine is busy.
-    request_queue_size = 128
-    daemon_threads = True
-
-
-class _Recorder:
-    def __init__(self):
-        self.lock = threading.Lock()
-        self.requests: List[Dict] = []
-
-    def add(self, item: Dict) -> None:
-        with self.lock:
-            self.requests.append(item)
-
-    def snapshot(self) -> List[Dict]:
-        with self.lock:
-            return list(self.requests)
-
-
-class FakeAloha(_Recorder):
-    """Stand-in for the downstream `aloha` service (GET /api/aloha-chaining -> JSON list)."""
-
-    def __init__(self):
-        super().__init__()
-        self.mode = "ok"
-        self.payload = ["Aloha mai fake-aloha", "Olá de fake-ola", "Bonjour de fake-bonjour"]
-        self.delay = 0.0
-        self.fail_first = 0  # drop this many upcoming requests without answering
-        self.raw = []        # mode "raw": byte strings written one after the other
-        fake = self
-
-        class Handler(BaseHTTPRequestHandler):
-            protocol_version = "HTTP/1.1"
-
-            def log_message(self, *a):
-                pass
-
-            def do_GET(self):
-                fake.add({"path": self.path, "headers": {k.lower(): v for k, v in self.headers.items()}, "time": time.time()})
-                if fake.delay:
-                    time.sleep(fake.delay)
-                mode = fake.mode
-                with fake.lock:
-                    if fake.fail_first > 0:
-                        fake.fail_first -= 1
-                        mode = "close"
-                if mode == "ok":
-                    body = json.dumps(fake.payload).encode()
-                    self._reply(200, body, "application/json")
-                elif mode == "chunked":
-                    body = json.dumps(fake.payload).encode()
-                    self.send_response(200)
-                    self.send_header("Content-Type", "application/json")
-                    self.send_header("Transfer-Encoding", "chunked")
-                    self.end_headers()
-                    half = len(body) // 2
-                    for part in (body[:half], body[half:]):
-                        self.wfile.write(b"%x\r\n" % len(part) + part + b"\r\n")
-                    self.wfile.write(b"0\r\n\r\n")
-                elif mode == "500":
-                    self._reply(500, b"boom", "text/plain")
-                elif mode == "404":
-                    self._reply(404, b"nope", "text/plain")
-                elif mode == "garbage":
-                    self._reply(200, b"<html>not json</html>", "text/html")
-                elif mode == "object":
-                    self._reply(200, b'{"greeting":"aloha"}', "application/json")
-                elif mode == "close":
-                    self.close_connection = True
-                    self.connection.close()
-                elif mode == "raw":
-                    # Arbitrary bytes (possibly in several writes), then the connection closes.
-                    for part in fake.raw:
-                        self.wfile.write(part)
-                        self.wfile.flush()
-                        time.sleep(0.02)
-                    self.close_connection = True
-                else:
-                    self._reply(200, b"[]", "application/json")
-
-            def _reply(self, status, body, ctype):
-                self.send_response(status)
-                self.send_header("Content-Type", ctype)
-                self.send_header("Content-Length", str(len(body)))
-                self.end_headers()
-                self.wfile.write(body)
-
-        self.httpd = _FakeServer(("127.0.0.1", 0), Handler)
-        self.httpd.daemon_threads = True
-        self.port = self.httpd.server_address[1]
-        self.thread = threading.Thread(target=self.httpd.serve_forever, daemon=True)
-        self.thread.start()
-
-    @property
-    def url(self) -> str:
-        return "http://127.0.0.1:%d/" % self.port
-
-    def stop(self):
-        self.httpd.shutdown()
-        self.httpd.server_close()
-
-
-class FakeZipkin(_Recorder):
-    """Stand-in for the Zipkin collector: records what is POSTed to /api/v1/spans."""
-
-    def __init__(self):
-        super().__init__()
-        self.status = 202
-        fake = self
-
-        class Handler(BaseHTTPRequestHandler):
-            protocol_version = "HTTP/1.1"
-
-            def log_message(self, *a):
-                pass
-
-            def do_POST(self):
-                n = int(self.headers.get("Content-Length", "0"))
-                body = self.rfile.read(n)
-                fake.add({"path": self.path, "content_type": self.headers.get("Content-Type"), "body": body})
-                self.send_response(fake.status)
-                self.send_header("Content-Length", "0")
-                self.end_headers()
-
-        self.httpd = _FakeServer(("127.0.0.1", 0), Handler)
-        self.httpd.daemon_threads = True
-        self.port = self.httpd.server_address[1]
-        self.thread = threading.Thread(target=self.httpd.serve_forever, daemon=True)
-        self.thread.start()
-
-    @property
-    def url(self) -> str:
-        return "http://127.0.0.1:%d" % self.port
-
-    def spans(self) -> List[Dict]:
-        out: List[Dict] = []
-        for rq in self.snapshot():
-            out.extend(json.loads(rq["body"]))
-        return out
-
-    def wait_for_spans(self, count: int, timeout: float = 5.0) -> List[Dict]:
-        deadline = time.time() + timeout
-        while time.time() < deadline:
-            spans = self.spans()
-            if len(spans) >= count:
-                return spans
-            time.sleep(0.05)
-        return self.spans()
-
-    def stop(self):
-        self.httpd.shutdown()
-        self.httpd.server_close()
+from hola_b200.fakes import FakeAloha, FakeZipkin  # noqa: E402,F401
 
 
 @pytest.fixture

@@ -16,109 +16,7 @@ from hola_b200 import client
 FALLBACK = "Aloha response (fallback)"
 
 
-class FakeDns:
-    """Answers A queries from a dict; everything else is NXDOMAIN. Optionally slow, silent, or
-    truncating (TC bit over UDP, full answer over TCP on the same port)."""
-
-    def __init__(self, records):
-        self.records = {k.lower(): v for k, v in records.items()}
-        self.delay = 0.0
-        self.silent = False
-        self.truncate_udp = False
-        self.queries = []
-        self.tcp_queries = []
-        # UDP and TCP on the same port number; another socket may hold the TCP side of the port
-        # the kernel picked for UDP, so try again until both can be had.
-        for _ in range(50):
-            self.sock = socket.socket(socket.AF_INET, socket.SOCK_DGRAM)
-            self.sock.bind(("127.0.0.1", 0))
-            self.port = self.sock.getsockname()[1]
-            self.tcp = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
-            self.tcp.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
-            try:
-                self.tcp.bind(("127.0.0.1", self.port))
-                break
-            except OSError:
-                self.sock.close()
-                self.tcp.close()
-        else:
-            raise RuntimeError("no port free for both UDP and TCP")
-        self.sock.settimeout(0.2)
-        self.tcp.listen(16)
-        self.tcp.settimeout(0.2)
-        self._stop = False
-        self.thread = threading.Thread(target=self._serve, daemon=True)
-        self.thread.start()
-        self.tcp_thread = threading.Thread(target=self._serve_tcp, daemon=True)
-        self.tcp_thread.start()
-
-    def _answer(self, data, truncated=False):
-        qid = data[:2]
-        pos, labels = 12, []
-        while data[pos]:
-            n = data[pos]
-            labels.append(data[pos + 1:pos + 1 + n].decode())
-            pos += 1 + n
-        name = ".".join(labels).lower()
-        question = data[12:pos + 5]
-        (qtype,) = struct.unpack(">H", data[pos + 1:pos + 3])
-        ip = self.records.get(name)
-        if truncated:
-            return name, qid + b"\x83\x80" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
-        if ip is None:
-            return name, qid + b"\x81\x83" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
-        is_v6 = ":" in ip
-        if (qtype == 1 and is_v6) or (qtype == 28 and not is_v6) or qtype not in (1, 28):
-            # The name exists but has no record of the requested type: NOERROR, zero answers.
-            return name, qid + b"\x81\x80" + b"\x00\x01\x00\x00\x00\x00\x00\x00" + question
-        rdata = socket.inet_pton(socket.AF_INET6, ip) if is_v6 else socket.inet_aton(ip)
-        answer = b"\xc0\x0c" + struct.pack(">HHIH", qtype, 1, 30, len(rdata)) + rdata
-        return name, qid + b"\x81\x80" + b"\x00\x01\x00\x01\x00\x00\x00\x00" + question + answer
-
-    def _serve(self):
-        while not self._stop:
-            try:
-                data, addr = self.sock.recvfrom(2048)
-            except socket.timeout:
-                continue
-            except OSError:
-                return
-            name, reply = self._answer(data, truncated=self.truncate_udp)
-            self.queries.append(name)
-            if self.silent:
-                continue
-            if self.delay:
-                time.sleep(self.delay)
-            self.sock.sendto(reply, addr)
-
-    def _serve_tcp(self):
-        while not self._stop:
-            try:
-                conn, _ = self.tcp.accept()
-            except socket.timeout:
-                continue
-            except OSError:
-                return
-            with conn:
-                conn.settimeout(2)
-                try:
-                    head = conn.recv(2)
-                    (n,) = struct.unpack(">H", head)
-                    data = b""
-                    while len(data) < n:
-                        data += conn.recv(n - len(data))
-                    name, reply = self._answer(data)
-                    self.tcp_queries.append(name)
-                    conn.sendall(struct.pack(">H", len(reply)) + reply)
-                except (OSError, struct.error):
-                    pass
-
-    def stop(self):
-        self._stop = True
-        self.thread.join(timeout=2)
-        self.tcp_thread.join(timeout=2)
-        self.sock.close()
-        self.tcp.close()
+from hola_b200.fakes import FakeDns  # noqa: E402
 
 
 @pytest.fixture
