@@ -403,9 +403,10 @@ class LoadThread {
             std::memmove(c.rbuf, c.rbuf + pos, c.rlen - pos);
             c.rlen -= pos;
         }
-        // Refill the pipeline / send what has become due.
+        // Refill the pipeline / send what has become due. The new request's clock starts at the
+        // moment it is written, not at the (earlier) time this batch of events was picked up.
         if (conn_period_ns_ == 0) {
-            fill_closed_loop(c, now);
+            fill_closed_loop(c, monotonic_ns());
         } else if (c.next_due_ns <= now) {
             schedule_open_loop(c, now);
         }
