@@ -285,10 +285,17 @@ Disposition HolaApp::handle(Worker& worker, Connection& conn, const RequestHead&
         return Disposition::kDone;
     }
 
-    if (path.size() > 9 && std::memcmp(path.data(), "/webjars/", 9) == 0 && !options_.webjars_dir.empty() &&
-        (rq.method == Method::kGet || rq.method == Method::kHead)) {
-        serve_static_file(st, conn, rq);
-        return Disposition::kDone;
+    if (path.size() > 9 && std::memcmp(path.data(), "/webjars/", 9) == 0 && (rq.method == Method::kGet || rq.method == Method::kHead)) {
+        if (!options_.webjars_dir.empty()) {
+            serve_static_file(st, conn, rq);
+            return Disposition::kDone;
+        }
+        // No Swagger-UI assets installed: the landing page's iframe still gets a working page.
+        if (path == "/webjars/swagger-ui/2.1.4/" || path == "/webjars/swagger-ui/2.1.4/index.html") {
+            append_response(&out, 200, "text/html", api_browser_html(), false, conn.closing(), rq.method == Method::kHead,
+                            worker.http_date());
+            return Disposition::kDone;
+        }
     }
 
     append_response(&out, 404, "text/html", undertow_error_page(404), false, conn.closing(), rq.method == Method::kHead,

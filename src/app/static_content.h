@@ -17,6 +17,8 @@ namespace hola {
 std::string_view index_html();
 std::string_view swagger_json();
 std::string_view swagger_yaml();
+// Self-contained page served where Swagger-UI's index would be when its assets are not installed.
+std::string_view api_browser_html();
 
 // Content type for a static file name, by extension (used for the optional webjars directory).
 std::string_view mime_type_for(std::string_view path);

@@ -231,8 +231,16 @@ def test_webjars_directory(hola_server, tmp_path):
     assert get(srv, "/webjars/../secret.txt").status == 404
     assert get(srv, "/webjars/%2e%2e/secret.txt").status == 404
     assert get(srv, "/webjars/swagger-ui/2.1.4/..%2f..%2f..%2fsecret.txt").status == 404
-    # Without --webjars-dir the assets are simply absent (they are not on the build box either).
-    assert get(hola_server(), "/webjars/swagger-ui/2.1.4/index.html").status == 404
+    # Without --webjars-dir the Swagger-UI assets are absent (they are not on the build box either),
+    # but the page the landing page frames is replaced by a built-in API browser, so "/" works.
+    bare = hola_server()
+    for target in ("/webjars/swagger-ui/2.1.4/?url=http://localhost:8080/api/swagger.json", "/webjars/swagger-ui/2.1.4/index.html"):
+        r = get(bare, target)
+        assert r.status == 200 and r.header("Content-Type") == "text/html"
+        assert b"Try it out" in r.body and b"fetch(specUrl)" in r.body
+        assert b"src=\"http" not in r.body and b"href=\"http" not in r.body  # self-contained: no external assets
+    assert get(bare, "/webjars/swagger-ui/2.1.4/swagger-ui.js").status == 404
+    assert get(bare, "/webjars/other/1.0/x.js").status == 404
 
 
 def test_cli_version_help_and_bad_args(native_build):
