@@ -141,6 +141,7 @@ void Connection::on_events(uint32_t events) {
             in_len_ += static_cast<size_t>(n);
             process_input();
             if (static_cast<size_t>(n) < space) break;  // socket drained
+            if (want_write_ && !streaming_) break;      // peer is not reading: stop producing for it
             continue;
         }
         if (n == 0) {
