@@ -31,6 +31,16 @@ int main(int argc, char** argv) {
             break;
     }
 
+    if (config.print_greeting) {
+        std::string body, error;
+        if (!resolve_greeting_once(config, &body, &error)) {
+            std::fprintf(stderr, "hola: %s\n", error.c_str());
+            return 1;
+        }
+        std::fwrite(body.data(), 1, body.size(), stdout);
+        return 0;
+    }
+
     // The worker threads must not receive the termination signals; this thread waits for them.
     sigset_t sigs;
     sigemptyset(&sigs);

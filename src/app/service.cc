@@ -48,6 +48,8 @@ std::string usage_text() {
            "                              for pinned, dedicated cores: trades idle CPU for lower latency)\n"
            "  --max-header-bytes N        request head limit (default 65536)\n"
            "  --log-config-reads          print the conf path on every config-file read, as the reference does\n"
+           "  --print-greeting            print what GET /api/hola would answer with this configuration and exit\n"
+           "                              (exit 1 if the pattern is one String.format would reject)\n"
            "  --verbose                   log downstream calls and request failures to stderr\n"
            "  --quiet                     no start-up/shutdown log lines\n"
            "  --version, --help\n";
@@ -158,6 +160,8 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
             cfg->app.verbose = true;
         } else if (a == "--quiet") {
             cfg->quiet = true;
+        } else if (a == "--print-greeting") {
+            cfg->print_greeting = true;
         } else if (a == "--version") {
             *message = std::string("hola ") + HOLA_VERSION + "\n";
             return ParseOutcome::kExitOk;
@@ -195,6 +199,42 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
     return ParseOutcome::kRun;
 }
 
+std::unique_ptr<ConfigResolver> build_config_resolver(const ServiceConfig& config) {
+    // Configuration layers, highest ordinal first (core/config.h).
+    std::unique_ptr<ConfigResolver> resolver(new ConfigResolver());
+    auto* system_props = new SystemPropertySource();
+    for (const auto& kv : config.system_properties) system_props->set(kv.first, kv.second);
+    auto* conf_source = new ConfFileSource(system_props);
+    if (config.log_config_reads) {
+        conf_source->set_on_read([](const std::string* path) {
+            std::printf("%s\n", path ? path->c_str() : "null");  // Configuration.java:28
+            std::fflush(stdout);
+        });
+    }
+    resolver->add_source(std::unique_ptr<ConfigSource>(system_props));
+    resolver->add_source(std::unique_ptr<ConfigSource>(new EnvironmentSource()));
+    if (!config.deltaspike_properties.empty()) {
+        resolver->add_source(std::unique_ptr<ConfigSource>(
+            new StaticPropertiesSource("META-INF/apache-deltaspike.properties", config.deltaspike_properties)));
+    }
+    resolver->add_source(std::unique_ptr<ConfigSource>(conf_source));
+    return resolver;
+}
+
+bool resolve_greeting_once(const ServiceConfig& config, std::string* body, std::string* error) {
+    std::unique_ptr<ConfigResolver> resolver = build_config_resolver(config);
+    const char* h = std::getenv("HOSTNAME");
+    GreetingService greeting(resolver.get(), h ? h : "unknown", nullptr);
+    greeting.poll(monotonic_ns());
+    const std::shared_ptr<const GreetingSnapshot> snap = greeting.snapshot();
+    if (!snap->ok) {
+        *error = "pattern \"" + snap->pattern + "\" cannot be formatted: " + snap->error;
+        return false;
+    }
+    *body = snap->text;
+    return true;
+}
+
 Service::Service(ServiceConfig config) : config_(std::move(config)) {}
 
 Service::~Service() { stop(); }
@@ -227,24 +267,7 @@ bool Service::start(std::string* error) {
         if (const char* z = std::getenv("ZIPKIN_SERVER_URL")) zipkin_url = z;
     }
 
-    // Configuration layers, highest ordinal first (core/config.h).
-    resolver_.reset(new ConfigResolver());
-    system_props_ = new SystemPropertySource();
-    for (const auto& kv : config_.system_properties) system_props_->set(kv.first, kv.second);
-    auto* conf_source = new ConfFileSource(system_props_);
-    if (config_.log_config_reads) {
-        conf_source->set_on_read([](const std::string* path) {
-            std::printf("%s\n", path ? path->c_str() : "null");  // Configuration.java:28
-            std::fflush(stdout);
-        });
-    }
-    resolver_->add_source(std::unique_ptr<ConfigSource>(system_props_));
-    resolver_->add_source(std::unique_ptr<ConfigSource>(new EnvironmentSource()));
-    if (!config_.deltaspike_properties.empty()) {
-        resolver_->add_source(std::unique_ptr<ConfigSource>(
-            new StaticPropertiesSource("META-INF/apache-deltaspike.properties", config_.deltaspike_properties)));
-    }
-    resolver_->add_source(std::unique_ptr<ConfigSource>(conf_source));
+    resolver_ = build_config_resolver(config_);
 
     greeting_.reset(new GreetingService(resolver_.get(), config_.app.hostname,
                                         [this](const std::string& m) { log("INFO", m); }));

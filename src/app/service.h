@@ -30,6 +30,7 @@ struct ServiceConfig {
     std::string deltaspike_properties;
     bool log_config_reads = false;
     bool quiet = false;
+    bool print_greeting = false;  // resolve and format the greeting once, print it, exit (see resolve_greeting_once)
     // Test hooks.
     std::vector<std::pair<std::string, std::string>> static_hosts;  // --resolve name=ipv4
     int zipkin_flush_ms = 1000;
@@ -41,6 +42,16 @@ enum class ParseOutcome { kRun, kExitOk, kExitUsage };
 ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceConfig* config, std::string* message);
 
 std::string usage_text();
+
+// The service's configuration stack (system properties > environment > optional static file >
+// the hot-reloaded `conf` file) for a parsed command line.
+std::unique_ptr<ConfigResolver> build_config_resolver(const ServiceConfig& config);
+
+// `hola --print-greeting`: what GET /api/hola would answer right now with this command line and
+// environment, without starting a server. False (with the JVM-style reason in *error) when the
+// configured pattern is one that would turn every request into a 500 - worth checking before a
+// properties file goes to production.
+bool resolve_greeting_once(const ServiceConfig& config, std::string* body, std::string* error);
 
 class Service {
  public:
@@ -62,7 +73,6 @@ class Service {
     void log(const char* level, const std::string& message) const;
 
     ServiceConfig config_;
-    SystemPropertySource* system_props_ = nullptr;  // owned by resolver_
     std::unique_ptr<ConfigResolver> resolver_;
     std::unique_ptr<GreetingService> greeting_;
     std::unique_ptr<Tracer> tracer_;

@@ -254,6 +254,14 @@ def test_cli_version_help_and_bad_args(native_build):
     assert out.returncode == 2 and "unknown argument" in out.stderr
     out = subprocess.run([exe, "--port", "99999"], capture_output=True, text=True)
     assert out.returncode == 2
+    # --print-greeting: the /api/hola body for a configuration, without starting a server.
+    env = {k: v for k, v in os.environ.items() if k not in ("HOSTNAME", "hello")}
+    out = subprocess.run([exe, "--print-greeting", "-Dconf=" + CONF], capture_output=True, env=dict(env, HOSTNAME="pod-3"))
+    assert out.returncode == 0 and out.stdout == b"Hola de pod-3 mediante el archivo de configuraciones\n"
+    out = subprocess.run([exe, "--print-greeting"], capture_output=True, env=env)
+    assert out.returncode == 0 and out.stdout == b"Hola de unknown"
+    out = subprocess.run([exe, "--print-greeting", "-Dhello=%d items"], capture_output=True, env=env)
+    assert out.returncode == 1 and b"IllegalFormatConversionException" in out.stderr
 
 
 def test_port_in_use_is_reported(hola_server, native_build):
