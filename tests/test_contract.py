@@ -84,7 +84,12 @@ def test_hola_hot_reload_within_five_seconds(hola_server, tmp_path):
             break
         time.sleep(0.1)
     assert body == b"Dos de unknown"
-    assert "New value Dos de %s for key hello." in srv.stderr  # logChanges(true), HolaResource.java:61
+    # logChanges(true), HolaResource.java:61. The line travels through a pipe and a reader thread:
+    # give it a moment.
+    deadline = time.time() + 3
+    while "New value Dos de %s for key hello." not in srv.stderr and time.time() < deadline:
+        time.sleep(0.05)
+    assert "New value Dos de %s for key hello." in srv.stderr
 
 
 def test_hola_source_precedence(hola_server, tmp_path):
