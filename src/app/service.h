@@ -32,7 +32,7 @@ struct ServiceConfig {
     bool quiet = false;
     bool print_greeting = false;  // resolve and format the greeting once, print it, exit (see resolve_greeting_once)
     // Test hooks.
-    std::vector<std::pair<std::string, std::string>> static_hosts;  // --resolve name=ipv4
+    std::vector<std::pair<std::string, std::string>> static_hosts;  // --resolve name=address (IPv4 or IPv6)
     int zipkin_flush_ms = 1000;
 };
 
