@@ -209,18 +209,26 @@ Disposition HolaApp::handle(Worker& worker, Connection& conn, const RequestHead&
             return Disposition::kDone;
         }
         if (rq.has_accept) {
+            // A client sends the same Accept header on every request; evaluate a header once and
+            // remember the verdicts for the three media types this service produces.
+            if (rq.accept != st.accept_header) {
+                st.accept_header.assign(rq.accept);
+                st.accept_text_plain = accept_allows(rq.accept, "text", "plain");
+                st.accept_json = accept_allows(rq.accept, "application", "json");
+                st.accept_yaml = accept_allows(rq.accept, "application", "yaml");
+            }
             bool ok = true;
             switch (route) {
                 case ApiRoute::kHola:
                 case ApiRoute::kHealth:
-                    ok = accept_allows(rq.accept, "text", "plain");
+                    ok = st.accept_text_plain;
                     break;
                 case ApiRoute::kChaining:
                 case ApiRoute::kSwaggerJson:
-                    ok = accept_allows(rq.accept, "application", "json");
+                    ok = st.accept_json;
                     break;
                 case ApiRoute::kSwaggerYaml:
-                    ok = accept_allows(rq.accept, "application", "yaml");
+                    ok = st.accept_yaml;
                     break;
                 case ApiRoute::kNone:
                     break;

@@ -58,6 +58,12 @@ struct HolaApp::WorkerState {
     size_t health_date_at = 0;
     int64_t health_second = -1;
 
+    // Verdicts for the most recently seen Accept header (see HolaApp::handle).
+    std::string accept_header;
+    bool accept_text_plain = true;
+    bool accept_json = true;
+    bool accept_yaml = true;
+
     std::unordered_map<uint64_t, StreamSub> streams;
 };
 

@@ -8,18 +8,19 @@
 namespace hola {
 namespace {
 
-inline bool is_token_char(unsigned char c) {
-    // RFC 7230 tchar
-    if (c >= '0' && c <= '9') return true;
-    if ((c | 0x20) >= 'a' && (c | 0x20) <= 'z') return true;
-    switch (c) {
-        case '!': case '#': case '$': case '%': case '&': case '\'': case '*': case '+':
-        case '-': case '.': case '^': case '_': case '`': case '|': case '~':
-            return true;
-        default:
-            return false;
+// RFC 7230 tchar, as a lookup table: header names are checked byte by byte on every request.
+struct TokenTable {
+    bool ok[256] = {};
+    constexpr TokenTable() {
+        for (int c = '0'; c <= '9'; ++c) ok[c] = true;
+        for (int c = 'a'; c <= 'z'; ++c) ok[c] = true;
+        for (int c = 'A'; c <= 'Z'; ++c) ok[c] = true;
+        for (char c : {'!', '#', '$', '%', '&', '\'', '*', '+', '-', '.', '^', '_', '`', '|', '~'}) ok[static_cast<unsigned char>(c)] = true;
     }
-}
+};
+constexpr TokenTable kToken;
+
+inline bool is_token_char(unsigned char c) { return kToken.ok[c]; }
 
 Method classify_method(std::string_view m) {
     switch (m.size()) {
@@ -46,20 +47,6 @@ Method classify_method(std::string_view m) {
             break;
     }
     return Method::kOther;
-}
-
-// Finds the end of the head: the first empty line. Returns the offset just past it, or 0.
-size_t find_head_end(const char* data, size_t len) {
-    size_t from = 0;
-    while (from < len) {
-        const char* nl = static_cast<const char*>(std::memchr(data + from, '\n', len - from));
-        if (!nl) return 0;
-        const size_t k = static_cast<size_t>(nl - data);
-        if (k + 1 < len && data[k + 1] == '\n') return k + 2;
-        if (k + 2 < len && data[k + 1] == '\r' && data[k + 2] == '\n') return k + 3;
-        from = k + 1;
-    }
-    return 0;
 }
 
 bool parse_content_length(std::string_view v, int64_t* out) {
@@ -89,33 +76,39 @@ struct HeaderLine {
     std::string_view value;
 };
 
-// Reads the header line starting at *pos; advances *pos past its line terminator. Returns
-// 1 for a header, 0 for the blank line, -1 for a malformed line.
-int next_header(const char* data, size_t head_len, size_t* pos, HeaderLine* out) {
-    size_t i = *pos;
-    if (i >= head_len) return 0;
+enum class Line { kHeader, kBlank, kIncomplete, kBad };
+
+// Reads the line starting at data[*pos] (header or the blank line that ends the head) from the
+// bytes available so far and advances *pos past its terminator. One pass: the end of the head is
+// discovered while the headers are being read, not by a separate scan.
+Line next_header(const char* data, size_t len, size_t* pos, HeaderLine* out) {
+    const size_t i = *pos;
+    if (i >= len) return Line::kIncomplete;
     if (data[i] == '\n') {
         *pos = i + 1;
-        return 0;
+        return Line::kBlank;
     }
-    if (data[i] == '\r' && i + 1 < head_len && data[i + 1] == '\n') {
-        *pos = i + 2;
-        return 0;
+    if (data[i] == '\r') {
+        if (i + 1 >= len) return Line::kIncomplete;
+        if (data[i + 1] == '\n') {
+            *pos = i + 2;
+            return Line::kBlank;
+        }
+        return Line::kBad;  // a header name cannot start with CR
     }
     const char* line = data + i;
-    const char* nl = static_cast<const char*>(std::memchr(line, '\n', head_len - i));
-    if (!nl) return -1;
+    const char* nl = static_cast<const char*>(std::memchr(line, '\n', len - i));
+    if (!nl) return Line::kIncomplete;
     size_t line_len = static_cast<size_t>(nl - line);
     *pos = i + line_len + 1;
     if (line_len > 0 && line[line_len - 1] == '\r') --line_len;
-    const char* colon = static_cast<const char*>(std::memchr(line, ':', line_len));
-    if (!colon || colon == line) return -1;
-    for (const char* p = line; p < colon; ++p) {
-        if (!is_token_char(static_cast<unsigned char>(*p))) return -1;
-    }
-    out->name = std::string_view(line, static_cast<size_t>(colon - line));
-    out->value = trim_ows(std::string_view(colon + 1, line_len - static_cast<size_t>(colon + 1 - line)));
-    return 1;
+    const char* p = line;
+    const char* line_end = line + line_len;
+    while (p < line_end && is_token_char(static_cast<unsigned char>(*p))) ++p;
+    if (p == line || p == line_end || *p != ':') return Line::kBad;
+    out->name = std::string_view(line, static_cast<size_t>(p - line));
+    out->value = trim_ows(std::string_view(p + 1, static_cast<size_t>(line_end - p - 1)));
+    return Line::kHeader;
 }
 
 }  // namespace
@@ -130,14 +123,11 @@ ParseStatus parse_request_head(const char* data, size_t len, RequestHead* out) {
     }
     const char* base = data + skip;
     const size_t avail = len - skip;
-    const size_t head_len = find_head_end(base, avail);
-    if (head_len == 0) return ParseStatus::kIncomplete;
-
-    *out = RequestHead();
-    out->head_len = skip + head_len;
 
     // Request line.
-    const char* nl = static_cast<const char*>(std::memchr(base, '\n', head_len));
+    const char* nl = static_cast<const char*>(std::memchr(base, '\n', avail));
+    if (!nl) return ParseStatus::kIncomplete;
+    *out = RequestHead();
     size_t line_len = static_cast<size_t>(nl - base);
     size_t pos = line_len + 1;
     if (line_len > 0 && base[line_len - 1] == '\r') --line_len;
@@ -182,9 +172,10 @@ ParseStatus parse_request_head(const char* data, size_t len, RequestHead* out) {
     bool saw_content_length = false;
     HeaderLine h;
     while (true) {
-        const int r = next_header(base, head_len, &pos, &h);
-        if (r == 0) break;
-        if (r < 0) return ParseStatus::kBad;
+        const Line r = next_header(base, avail, &pos, &h);
+        if (r == Line::kBlank) break;
+        if (r == Line::kIncomplete) return ParseStatus::kIncomplete;
+        if (r == Line::kBad) return ParseStatus::kBad;
         switch (h.name.size()) {
             case 4:
                 if (ascii_iequals(h.name, "host")) out->host = h.value;
@@ -199,7 +190,9 @@ ParseStatus parse_request_head(const char* data, size_t len, RequestHead* out) {
                 break;
             case 10:
                 if (ascii_iequals(h.name, "connection")) {
-                    if (contains_token(h.value, "close")) {
+                    if (ascii_iequals(h.value, "keep-alive")) {  // by far the usual value
+                        out->keep_alive = true;
+                    } else if (contains_token(h.value, "close")) {
                         out->keep_alive = false;
                     } else if (contains_token(h.value, "keep-alive")) {
                         out->keep_alive = true;
@@ -238,15 +231,14 @@ ParseStatus parse_request_head(const char* data, size_t len, RequestHead* out) {
         }
     }
     if (out->chunked) out->content_length = -1;  // RFC 7230 3.3.3: Transfer-Encoding wins
+    out->head_len = skip + pos;
     return ParseStatus::kComplete;
 }
 
 ParseStatus parse_response_head(const char* data, size_t len, ResponseHead* out) {
-    const size_t head_len = find_head_end(data, len);
-    if (head_len == 0) return ParseStatus::kIncomplete;
+    const char* nl = static_cast<const char*>(std::memchr(data, '\n', len));
+    if (!nl) return ParseStatus::kIncomplete;
     *out = ResponseHead();
-    out->head_len = head_len;
-    const char* nl = static_cast<const char*>(std::memchr(data, '\n', head_len));
     size_t line_len = static_cast<size_t>(nl - data);
     size_t pos = line_len + 1;
     if (line_len > 0 && data[line_len - 1] == '\r') --line_len;
@@ -270,13 +262,16 @@ ParseStatus parse_response_head(const char* data, size_t len, ResponseHead* out)
     out->status = status;
     HeaderLine h;
     while (true) {
-        const int r = next_header(data, head_len, &pos, &h);
-        if (r == 0) break;
-        if (r < 0) return ParseStatus::kBad;
+        const Line r = next_header(data, len, &pos, &h);
+        if (r == Line::kBlank) break;
+        if (r == Line::kIncomplete) return ParseStatus::kIncomplete;
+        if (r == Line::kBad) return ParseStatus::kBad;
         switch (h.name.size()) {
             case 10:
                 if (ascii_iequals(h.name, "connection")) {
-                    if (contains_token(h.value, "close")) {
+                    if (ascii_iequals(h.value, "keep-alive")) {  // by far the usual value
+                        out->keep_alive = true;
+                    } else if (contains_token(h.value, "close")) {
                         out->keep_alive = false;
                     } else if (contains_token(h.value, "keep-alive")) {
                         out->keep_alive = true;
@@ -301,6 +296,7 @@ ParseStatus parse_response_head(const char* data, size_t len, ResponseHead* out)
         }
     }
     if (out->chunked) out->content_length = -1;
+    out->head_len = pos;
     return ParseStatus::kComplete;
 }
 
