@@ -418,6 +418,39 @@ TEST(http_request_incomplete_and_bad) {
     }
 }
 
+TEST(http_request_single_pass_edges) {
+    RequestHead h;
+    // A malformed line is reported as soon as it is complete, even if the head is not.
+    std::string raw = "GET /x HTTP/1.1\r\nBad Name: v\r\nHost: not-yet-termina";
+    CHECK(parse_request_head(raw.data(), raw.size(), &h) == ParseStatus::kBad);
+    // CR that is not part of a line end.
+    raw = "GET /x HTTP/1.1\r\n\rX: y\r\n\r\n";
+    CHECK(parse_request_head(raw.data(), raw.size(), &h) == ParseStatus::kBad);
+    // Head ends right at the buffer end, with and without CR; a lone trailing CR is "need more".
+    raw = "GET /x HTTP/1.1\r\nHost: a\r\n\r";
+    CHECK(parse_request_head(raw.data(), raw.size(), &h) == ParseStatus::kIncomplete);
+    raw += "\n";
+    CHECK(parse_request_head(raw.data(), raw.size(), &h) == ParseStatus::kComplete);
+    CHECK_EQ(h.head_len, raw.size());
+    raw = "GET /x HTTP/1.1\nHost: a\n\nGET /y HTTP/1.1\n\n";
+    CHECK(parse_request_head(raw.data(), raw.size(), &h) == ParseStatus::kComplete);
+    CHECK_EQ(h.head_len, size_t{25});
+    // Every token character is accepted in a header name, nothing else is.
+    raw = "GET /x HTTP/1.1\r\n!#$%&'*+-.^_`|~09azAZ: ok\r\n\r\n";
+    CHECK(parse_request_head(raw.data(), raw.size(), &h) == ParseStatus::kComplete);
+    for (const char* bad : {"(", ")", "<", ">", "@", ",", ";", "\\", "\"", "/", "[", "]", "?", "=", "{", "}", " ", "\t", "\x7f", "\x80"}) {
+        raw = std::string("GET /x HTTP/1.1\r\nX") + bad + "Y: v\r\n\r\n";
+        CHECK(parse_request_head(raw.data(), raw.size(), &h) == ParseStatus::kBad);
+    }
+    // Connection header: usual value, lists, case.
+    raw = "GET /x HTTP/1.0\r\nConnection: KEEP-ALIVE\r\n\r\n";
+    CHECK(parse_request_head(raw.data(), raw.size(), &h) == ParseStatus::kComplete);
+    CHECK(h.keep_alive);
+    raw = "GET /x HTTP/1.1\r\nConnection: keep-alive, close\r\n\r\n";
+    CHECK(parse_request_head(raw.data(), raw.size(), &h) == ParseStatus::kComplete);
+    CHECK(!h.keep_alive);
+}
+
 TEST(http_response_and_chunked) {
     ResponseHead r;
     std::string raw = "HTTP/1.1 200 OK\r\nContent-Type: application/json\r\nContent-Length: 9\r\n\r\n[\"aloha\"]";
