@@ -206,7 +206,10 @@ def test_rolling_restart_loses_no_request(hola_server):
     import json
     import subprocess
     from hola_b200 import paths
-    old = hola_server(threads=2)
+    # A generous linger: on a starved machine a busy client can look idle for longer than the
+    # default 100 ms, and a connection closed under a request in flight is the one thing that
+    # would make this hand-over lossy.
+    old = hola_server(threads=2, args=["--drain-linger-ms", "1000"])
     load = subprocess.Popen([str(paths().hola_load), "--json", "-c", "16", "-d", "3", "-w", "0", "-t", "2", "--expect-body",
                              "Hola de unknown", "http://127.0.0.1:%d/api/hola" % old.port], stdout=subprocess.PIPE, text=True)
     time.sleep(1.0)
