@@ -131,6 +131,25 @@ def test_format_width_pads_like_python(width, host, left):
     assert native.java_format(spec, host) == expected.encode()
 
 
+@settings(max_examples=300, deadline=None)
+@given(st.booleans(), st.one_of(st.none(), st.integers(min_value=1, max_value=30)), st.one_of(st.none(), st.integers(min_value=0, max_value=30)),
+       st.text(alphabet=string.ascii_letters + string.digits + " éßñ€中", max_size=25), st.sampled_from(["s", "S"]))
+def test_format_width_and_precision_agree_with_python(left, width, precision, host, conv):
+    """For BMP text, Java's %[-][w][.p]s and Python's are the same function (width and precision
+    count characters; precision truncates before padding). %S additionally upper-cases."""
+    if left and width is None:
+        return  # '-' without a width is an error on the JVM (covered elsewhere)
+    spec = "%" + ("-" if left else "") + ("" if width is None else str(width)) + ("" if precision is None else "." + str(precision))
+    expected = (spec + "s") % host
+    if conv == "S":
+        # str.upper() and String.toUpperCase() agree on this alphabet (including ß -> SS); upper-casing
+        # happens after truncation, before padding.
+        cut = host if precision is None else host[:precision]
+        up = cut.upper()
+        expected = up.ljust(width) if (left and width) else (up.rjust(width) if width else up)
+    assert native.java_format("[" + spec + conv + "]", host) == ("[" + expected + "]").encode()
+
+
 @pytest.mark.parametrize("pattern,exc", [
     ("%s %s", "MissingFormatArgumentException"),
     ("%d", "IllegalFormatConversionException"),
