@@ -75,7 +75,7 @@ def partition(cpus: Sequence[int], parts: int) -> List[List[int]]:
 
 
 def run_instance(index: int, cpus: Sequence[int], steps: int, warmup: int, mode: str, max_cpus: int,
-                 server_share: float, results: Dict[int, Dict]) -> None:
+                 server_share: float, results: Dict[int, Dict], half_load_seconds: int = 0) -> None:
     from hola_b200 import loadgen
     from hola_b200.server import HolaServer
     from hola_b200.utils import split_cpus
@@ -103,6 +103,18 @@ def run_instance(index: int, cpus: Sequence[int], steps: int, warmup: int, mode:
         report["load_cpus"] = list(load_cpus)
         report["server_threads"] = server_threads
         report["startup_s"] = srv.startup_seconds
+        if half_load_seconds > 0:
+            # Context for the headline, outside its timed region: the same 64 connections driven
+            # open-loop at half the measured throughput, latency taken from the scheduled send time.
+            # This is what a client sees when the service is busy but not saturated.
+            try:
+                half = loadgen.run(srv.base_url + "/api/hola", connections=CONNECTIONS, duration=half_load_seconds, warmup=1,
+                                   interval=1.0, threads=load_threads, cpus=load_cpus, expect_body=expect, rate=report["rps"] / 2)
+                report["half_load"] = {"offered_rps": round(report["rps"] / 2, 1), "achieved_rps": half["rps"],
+                                       "p50_us": half["latency_us"]["p50"], "p99_us": half["latency_us"]["p99"],
+                                       "p999_us": half["latency_us"]["p999"], "seconds": half_load_seconds}
+            except Exception as exc:  # noqa: BLE001 - additional information only
+                report["half_load"] = {"error": "%s: %s" % (type(exc).__name__, exc)}
     results[index] = report
 
 
@@ -119,6 +131,9 @@ def main() -> int:
                     help="cap on CPUs used per instance (server + generator)")
     ap.add_argument("--server-share", type=float, default=float(os.environ.get("HOLA_BENCH_SERVER_SHARE", "0.5")),
                     help="fraction of an instance's CPUs given to the server (rest: load generator)")
+    ap.add_argument("--half-load-seconds", type=int, default=5,
+                    help="after the timed run (N=1 only): an open-loop run at half the measured rate for this many "
+                         "seconds, reported as `half_load` (0 to skip)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -155,7 +170,8 @@ def main() -> int:
     t0 = time.monotonic()
     def guarded(i: int) -> None:
         try:
-            run_instance(i, slices[i % len(slices)], args.steps, args.warmup, args.mode, args.max_cpus, args.server_share, results)
+            run_instance(i, slices[i % len(slices)], args.steps, args.warmup, args.mode, args.max_cpus, args.server_share, results,
+                         half_load_seconds=args.half_load_seconds if (n == 1 and not distributed) else 0)
         except Exception as exc:  # noqa: BLE001 - reported below, on every rank
             results[i] = {"error": "%s: %s" % (type(exc).__name__, exc)}
 
@@ -261,6 +277,7 @@ def main() -> int:
                     "response is read and checked; no device is involved, so there is no device-timed number to contrast it with",
             "wire_bytes_per_step": int(local_bytes / max(1, args.steps)),
         },
+        "half_load": first.get("half_load"),
         "gpu_launches": 0,
         "gpu_note": "CPU-only service: the reference has no kernels, tensors or collectives (SURVEY.md 2.3); none were invented",
     }
