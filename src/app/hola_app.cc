@@ -111,6 +111,7 @@ HolaApp::HolaApp(AppOptions options, GreetingService* greeting, Tracer* tracer, 
       command_("AlohaService#aloha()", "http://" + authority_of(options_) + "/", "http://" + authority_of(options_) + "/",
                options_.breaker) {
     const std::string authority = authority_of(options_);
+    aloha_stand_in_body_ = json_encode_string_list({std::string("Aloha mai ") + options_.hostname});
     aloha_url_ = "http://" + authority + options_.aloha_path;
     aloha_request_prefix_ = "GET " + options_.aloha_path + " HTTP/1.1\r\nHost: " + authority +
                             "\r\nAccept: */*\r\nConnection: keep-alive\r\nUser-Agent: hola-b200\r\n";
@@ -189,6 +190,13 @@ Disposition HolaApp::handle(Worker& worker, Connection& conn, const RequestHead&
 
     // The JAX-RS servlet is mapped to /api/* (JaxRsActivator.java:30), which also covers "/api".
     if ((path.size() >= 5 && std::memcmp(path.data(), "/api/", 5) == 0) || path == "/api") {
+        // Stand-in for the next service of the demo chain (--serve-aloha): lets two hola processes
+        // be chained for demos and for measuring the downstream path without a JVM or Vert.x.
+        if (options_.serve_aloha && path == "/api/aloha-chaining" && (rq.method == Method::kGet || rq.method == Method::kHead)) {
+            append_response(&out, 200, kJson, aloha_stand_in_body_, true, conn.closing(), rq.method == Method::kHead,
+                            worker.http_date());
+            return Disposition::kDone;
+        }
         const ApiRoute route = match_api(path.substr(4));
         if (route == ApiRoute::kNone) {
             // The message quotes the request URL and goes out as text/html: escape it, or any

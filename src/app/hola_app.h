@@ -46,6 +46,7 @@ struct AppOptions {
     int stream_max_connections = 5;               // hystrix.stream.maxConcurrentConnections default
     int stream_default_delay_ms = 500;
     bool verbose = false;
+    bool serve_aloha = false;  // also answer GET /api/aloha-chaining like the next service of the demo would
 };
 
 class HolaApp final : public Application {
@@ -101,6 +102,7 @@ class HolaApp final : public Application {
     std::atomic<int> stream_connections_{0};
     std::string aloha_request_prefix_;  // request line + fixed headers, B3 headers are appended
     std::string aloha_url_;             // for the client span's http.url tag
+    std::string aloha_stand_in_body_;   // what --serve-aloha answers on /api/aloha-chaining
 };
 
 }  // namespace hola

@@ -48,6 +48,8 @@ std::string usage_text() {
            "                              for pinned, dedicated cores: trades idle CPU for lower latency)\n"
            "  --max-header-bytes N        request head limit (default 65536)\n"
            "  --log-config-reads          print the conf path on every config-file read, as the reference does\n"
+           "  --serve-aloha               also answer GET /api/aloha-chaining with [\"Aloha mai <HOSTNAME>\"]: a stand-in\n"
+           "                              for the next service of the demo chain (point another hola at it)\n"
            "  --print-greeting            print what GET /api/hola would answer with this configuration and exit\n"
            "                              (exit 1 if the pattern is one String.format would reject)\n"
            "  --verbose                   log downstream calls and request failures to stderr\n"
@@ -160,6 +162,8 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
             cfg->app.verbose = true;
         } else if (a == "--quiet") {
             cfg->quiet = true;
+        } else if (a == "--serve-aloha") {
+            cfg->app.serve_aloha = true;
         } else if (a == "--print-greeting") {
             cfg->print_greeting = true;
         } else if (a == "--version") {

@@ -91,6 +91,14 @@ class HttpClient::Conn final : public EventHandler {
  private:
     friend class HttpClient;
 
+    // A keep-alive connection spends its life waiting for input; the interest set only changes
+    // around connect() and when a write would block, so most requests need no epoll_ctl at all.
+    void set_interest(uint32_t events) {
+        if (events == registered_) return;
+        registered_ = events;
+        client_->loop_->modify(fd_, events, this);
+    }
+
     void write_request() {
         const std::string& r = req_->request;
         while (sent_ < r.size()) {
@@ -101,14 +109,14 @@ class HttpClient::Conn final : public EventHandler {
             }
             if (n < 0 && errno == EINTR) continue;
             if (n < 0 && (errno == EAGAIN || errno == EWOULDBLOCK)) {
-                client_->loop_->modify(fd_, EPOLLOUT | EPOLLRDHUP, this);
+                set_interest(EPOLLOUT | EPOLLRDHUP);
                 return;
             }
             client_->retry_or_fail(this, ClientResult::Code::kIoError);
             return;
         }
         state_ = State::kReading;
-        client_->loop_->modify(fd_, EPOLLIN | EPOLLRDHUP, this);
+        set_interest(EPOLLIN | EPOLLRDHUP);
     }
 
     void read_response() {
@@ -230,6 +238,7 @@ class HttpClient::Conn final : public EventHandler {
     int fd_;
     std::string key_;
     State state_ = State::kConnecting;
+    uint32_t registered_ = 0;
     std::shared_ptr<Pending> req_;
     bool reused_ = false;
     bool got_bytes_ = false;
@@ -331,7 +340,8 @@ void HttpClient::start_connect(const std::shared_ptr<Pending>& p, const IpAddres
     conns_.insert(c);
     c->begin(p, false);
     c->state_ = Conn::State::kConnecting;
-    if (!loop_->add(fd, EPOLLOUT | EPOLLRDHUP, c)) {
+    c->registered_ = EPOLLOUT | EPOLLRDHUP;
+    if (!loop_->add(fd, c->registered_, c)) {
         retry_or_fail(c, ClientResult::Code::kConnectFailed);
     }
 }
@@ -366,7 +376,7 @@ void HttpClient::finish(Conn* conn, ClientResult&& result, bool reusable) {
         auto& list = idle_[conn->key_];
         if (list.size() < max_idle_per_host_) {
             conn->state_ = Conn::State::kIdle;
-            loop_->modify(conn->fd_, EPOLLIN | EPOLLRDHUP, conn);
+            conn->set_interest(EPOLLIN | EPOLLRDHUP);
             list.push_back(conn);
             pooled = true;
         }

@@ -39,7 +39,7 @@ class HttpClient {
     using Callback = std::function<void(ClientResult&&)>;
     using RequestId = uint64_t;
 
-    HttpClient(EventLoop* loop, Resolver* resolver, size_t max_idle_per_host = 16,
+    HttpClient(EventLoop* loop, Resolver* resolver, size_t max_idle_per_host = 64,
                size_t max_response_bytes = 1 << 20);
     ~HttpClient();
 

@@ -238,6 +238,19 @@ def test_fallback_disabled_turns_failures_into_500(hola_server, fake_aloha):
     assert json.loads(chain(srv).body) == ["Hola de unknown"]  # an empty downstream list is not a failure
 
 
+def test_two_hola_processes_chained(hola_server):
+    """--serve-aloha makes a hola process stand in for the next service of the demo chain."""
+    downstream = hola_server(args=["--serve-aloha"], env={"HOSTNAME": "aloha-1"})
+    upstream = hola_server(args=["--aloha-url", downstream.base_url + "/"], env={"HOSTNAME": "hola-1"})
+    with client.Connection("127.0.0.1", upstream.port) as c:
+        for _ in range(20):
+            r = c.request("GET", "/api/hola-chaining")
+            assert r.status == 200 and json.loads(r.body) == ["Hola de hola-1", "Aloha mai aloha-1"]
+    # Without the flag the endpoint does not exist.
+    assert client.get("127.0.0.1", upstream.port, "/api/aloha-chaining").status == 404
+    assert json.loads(client.get("127.0.0.1", downstream.port, "/api/aloha-chaining").body) == ["Aloha mai aloha-1"]
+
+
 def test_head_on_chaining(hola_server, fake_aloha):
     srv = hola_server(args=["--aloha-url", fake_aloha.url])
     r = client.get("127.0.0.1", srv.port, "/api/hola-chaining", method="HEAD")
