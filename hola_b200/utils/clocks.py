@@ -7,6 +7,7 @@ which is sampled from /proc/cpuinfo alongside.
 """
 from __future__ import annotations
 
+import os
 import shutil
 import statistics
 import subprocess
@@ -38,7 +39,7 @@ def cpu_info() -> Dict:
 class ClockSampler:
     """Samples nvidia-smi (if present) and /proc/cpuinfo every ``period`` seconds in a thread."""
 
-    def __init__(self, period: float = 0.5):
+    def __init__(self, period: float = 2.0):
         self.period = period
         self.smi = shutil.which("nvidia-smi")
         self._stop = threading.Event()
@@ -52,8 +53,12 @@ class ClockSampler:
         if not self.smi:
             return
         try:
+            # nvidia-smi is a heavy process (tens of ms of CPU per call) and every CPU of the box is
+            # busy with the pinned server and generator threads: run it at the lowest priority so
+            # that it fills gaps instead of stalling a loop that is being measured.
             out = subprocess.run([self.smi, "--query-gpu=" + _QUERY, "--format=csv,noheader,nounits", "-i", "0"],
-                                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=5).stdout
+                                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=10,
+                                 preexec_fn=lambda: os.nice(19)).stdout
         except (OSError, subprocess.TimeoutExpired):
             return
         for line in out.strip().splitlines():
