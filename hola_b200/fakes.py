@@ -183,6 +183,7 @@ class FakeDns:
         self.delay = 0.0
         self.silent = False
         self.truncate_udp = False
+        self.stray_first = None  # (name, ip): first send an answer to this *other* question under the query's id
         self.queries = []
         self.tcp_queries = []
         # UDP and TCP on the same port number; another socket may hold the TCP side of the port
@@ -247,6 +248,15 @@ class FakeDns:
                 continue
             if self.delay:
                 time.sleep(self.delay)
+            if self.stray_first:
+                # What an off-path spoofer who guessed the id would send: the right id, somebody
+                # else's question. A resolver must ignore it and wait for the real answer.
+                other, ip = self.stray_first
+                qname = b"".join(bytes([len(l)]) + l.encode() for l in other.split(".")) + b"\x00"
+                qtype = data[-4:-2]
+                self.sock.sendto(data[:2] + b"\x81\x80" + b"\x00\x01\x00\x01\x00\x00\x00\x00" + qname + qtype + b"\x00\x01" +
+                                 b"\xc0\x0c" + qtype + b"\x00\x01" + struct.pack(">IH", 30, 4) + socket.inet_aton(ip), addr)
+                time.sleep(0.02)
             self.sock.sendto(reply, addr)
 
     def _serve_tcp(self):

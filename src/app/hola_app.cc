@@ -1,8 +1,10 @@
 #include "app/hola_app.h"
 
+#include <limits.h>
 #include <sys/stat.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "app/hola_app_internal.h"
@@ -93,6 +95,10 @@ ApiRoute match_api(std::string_view sub) {
 
 namespace {
 
+int64_t mtime_ns_of(const struct stat& sb) {
+    return static_cast<int64_t>(sb.st_mtim.tv_sec) * 1000000000ll + sb.st_mtim.tv_nsec;
+}
+
 // host:port as it appears in URLs and Host headers (IPv6 literals go in brackets).
 std::string authority_of(const AppOptions& o) {
     const bool v6_literal = o.aloha_host.find(':') != std::string::npos;
@@ -113,6 +119,11 @@ HolaApp::HolaApp(AppOptions options, GreetingService* greeting, Tracer* tracer, 
     const std::string authority = authority_of(options_);
     aloha_stand_in_body_ = json_encode_string_list({std::string("Aloha mai ") + options_.hostname});
     aloha_url_ = "http://" + authority + options_.aloha_path;
+    if (!options_.webjars_dir.empty()) {
+        char resolved[PATH_MAX];
+        webjars_root_ = realpath(options_.webjars_dir.c_str(), resolved) ? std::string(resolved) : options_.webjars_dir;
+        while (webjars_root_.size() > 1 && webjars_root_.back() == '/') webjars_root_.pop_back();
+    }
     aloha_request_prefix_ = "GET " + options_.aloha_path + " HTTP/1.1\r\nHost: " + authority +
                             "\r\nAccept: */*\r\nConnection: keep-alive\r\nUser-Agent: hola-b200\r\n";
 }
@@ -355,41 +366,88 @@ Disposition HolaApp::serve_hola(WorkerState& st, Connection& conn, const Request
     return Disposition::kDone;
 }
 
+// Static assets under --webjars-dir (the Swagger-UI webjar of the reference, pom.xml:207-211).
+//
+// Containment: the decoded path is resolved with realpath() and must stay below the resolved
+// root, so neither ".." nor a symbolic link inside the directory can lead out of it.
+// Cost: a request normally costs one realpath() and one stat() - both answered from the kernel's
+// dentry cache - and the body comes from an in-memory copy keyed by path, size and mtime. Only a
+// file that changed (or was never seen) is read, in one go, on the event-loop thread; files above
+// kStaticMaxFile are refused rather than allowed to stall the loop.
 void HolaApp::serve_static_file(WorkerState& st, Connection& conn, const RequestHead& rq) {
+    constexpr off_t kStaticMaxFile = 16 << 20;
+    constexpr size_t kStaticCacheBytes = 64u << 20;
     Worker& worker = *st.worker;
     const bool head_only = rq.method == Method::kHead;
     std::string rel;
     bool ok = percent_decode(rq.path.substr(8), &rel);  // keeps the leading '/'
     if (ok) {
-        // No escaping the directory, no hidden files, no NULs.
+        // No hidden files, no NULs, no backslashes (the resolved-path check below does the rest).
         if (rel.find('\0') != std::string::npos || rel.find("/.") != std::string::npos || rel.find('\\') != std::string::npos)
             ok = false;
     }
     std::string full;
+    struct stat sb{};
     if (ok) {
-        full = options_.webjars_dir + rel;
-        struct stat sb;
-        if (stat(full.c_str(), &sb) != 0) {
-            ok = false;
-        } else if (S_ISDIR(sb.st_mode)) {
-            if (full.back() != '/') full.push_back('/');
-            full.append("index.html");
-            ok = stat(full.c_str(), &sb) == 0 && S_ISREG(sb.st_mode);
-        } else if (!S_ISREG(sb.st_mode)) {
-            ok = false;
-        }
-        if (ok && sb.st_size > (16 << 20)) ok = false;
-    }
-    std::string body;
-    if (ok) {
-        FILE* f = std::fopen(full.c_str(), "rb");
-        if (!f) {
+        char resolved[PATH_MAX];
+        const std::string candidate = webjars_root_ + rel;
+        if (!realpath(candidate.c_str(), resolved)) {
             ok = false;
         } else {
-            char buf[16384];
-            size_t got;
-            while ((got = std::fread(buf, 1, sizeof buf, f)) > 0) body.append(buf, got);
-            std::fclose(f);
+            full = resolved;
+            if (stat(full.c_str(), &sb) != 0) {
+                ok = false;
+            } else if (S_ISDIR(sb.st_mode)) {
+                const std::string index = full + "/index.html";
+                ok = realpath(index.c_str(), resolved) != nullptr;
+                if (ok) {
+                    full = resolved;
+                    ok = stat(full.c_str(), &sb) == 0;
+                }
+            }
+        }
+        if (ok && !S_ISREG(sb.st_mode)) ok = false;
+        if (ok && (full.size() <= webjars_root_.size() || full.compare(0, webjars_root_.size(), webjars_root_) != 0 ||
+                   full[webjars_root_.size()] != '/'))
+            ok = false;  // a link (or the root's own parent) led outside the directory
+        if (ok && sb.st_size > kStaticMaxFile) ok = false;
+    }
+    std::shared_ptr<const StaticFile> file;
+    if (ok) {
+        {
+            std::lock_guard<std::mutex> lock(static_mu_);
+            auto it = static_cache_.find(full);
+            if (it != static_cache_.end() && it->second->size == sb.st_size && it->second->mtime_ns == mtime_ns_of(sb))
+                file = it->second;
+        }
+        if (!file) {
+            auto fresh = std::make_shared<StaticFile>();
+            fresh->size = sb.st_size;
+            fresh->mtime_ns = mtime_ns_of(sb);
+            FILE* f = std::fopen(full.c_str(), "rb");
+            if (!f) {
+                ok = false;
+            } else {
+                fresh->body.reserve(static_cast<size_t>(sb.st_size));
+                char buf[65536];
+                size_t got;
+                while ((got = std::fread(buf, 1, sizeof buf, f)) > 0 && fresh->body.size() <= static_cast<size_t>(kStaticMaxFile))
+                    fresh->body.append(buf, got);
+                std::fclose(f);
+                file = fresh;
+                std::lock_guard<std::mutex> lock(static_mu_);
+                auto old = static_cache_.find(full);
+                if (old != static_cache_.end()) {
+                    static_cache_bytes_ -= old->second->body.size();
+                    static_cache_.erase(old);
+                }
+                if (static_cache_bytes_ + fresh->body.size() > kStaticCacheBytes) {  // crude but bounded: start over
+                    static_cache_.clear();
+                    static_cache_bytes_ = 0;
+                }
+                static_cache_bytes_ += fresh->body.size();
+                static_cache_.emplace(full, fresh);
+            }
         }
     }
     if (!ok) {
@@ -397,7 +455,7 @@ void HolaApp::serve_static_file(WorkerState& st, Connection& conn, const Request
                         worker.http_date());
         return;
     }
-    append_response(&conn.out(), 200, mime_type_for(full), body, false, conn.closing(), head_only, worker.http_date());
+    append_response(&conn.out(), 200, mime_type_for(full), file->body, false, conn.closing(), head_only, worker.http_date());
 }
 
 }  // namespace hola

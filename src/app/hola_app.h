@@ -103,6 +103,17 @@ class HolaApp final : public Application {
     std::string aloha_request_prefix_;  // request line + fixed headers, B3 headers are appended
     std::string aloha_url_;             // for the client span's http.url tag
     std::string aloha_stand_in_body_;   // what --serve-aloha answers on /api/aloha-chaining
+
+    // /webjars/**: resolved root and an in-memory copy of the files served so far.
+    struct StaticFile {
+        int64_t size = 0;
+        int64_t mtime_ns = 0;
+        std::string body;
+    };
+    std::string webjars_root_;
+    std::mutex static_mu_;
+    std::unordered_map<std::string, std::shared_ptr<const StaticFile>> static_cache_;
+    size_t static_cache_bytes_ = 0;
 };
 
 }  // namespace hola

@@ -146,6 +146,9 @@ TracerStats Tracer::stats() const {
     s.spans_dropped = spans_failed_.load(std::memory_order_relaxed);
     s.posts_ok = posts_ok_.load(std::memory_order_relaxed);
     s.posts_failed = posts_failed_.load(std::memory_order_relaxed);
+    // register_producer() appends to rings_ from the worker threads as they start; a host that
+    // asks for statistics right after starting the service must not walk the vector meanwhile.
+    std::lock_guard<std::mutex> lock(mu_);
     for (const auto& r : rings_) s.spans_dropped += r->dropped();
     return s;
 }

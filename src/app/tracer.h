@@ -103,7 +103,7 @@ class Tracer {
     const size_t ring_capacity_;
     const size_t max_batch_;
 
-    std::mutex mu_;
+    mutable std::mutex mu_;
     std::condition_variable cv_;
     bool stop_ = false;
     std::atomic<bool> stopping_{false};  // same as stop_, readable without the lock

@@ -255,11 +255,30 @@ bool read_name(const uint8_t* d, size_t len, size_t pos, std::string* out) {
 
 }  // namespace
 
-DnsStatus dns_parse_response(const uint8_t* d, size_t len, uint16_t id, IpAddress* out, bool* truncated, uint16_t qtype) {
+DnsStatus dns_parse_response(const uint8_t* d, size_t len, uint16_t id, IpAddress* out, bool* truncated, uint16_t qtype,
+                             const std::string* asked_name) {
     if (truncated) *truncated = false;
     if (len < 12) return DnsStatus::kError;
     if (static_cast<uint16_t>((d[0] << 8) | d[1]) != id) return DnsStatus::kError;
     if (!(d[2] & 0x80)) return DnsStatus::kError;  // not a response
+    if (asked_name) {
+        // The 16-bit id is all that ties a datagram to a query otherwise. The question section of
+        // a genuine response repeats what was asked: one question, same name (case-insensitive),
+        // same type, class IN. Anything else answers some other question - also when its rcode
+        // says NXDOMAIN - and must not be taken for the answer to this one.
+        if (((d[4] << 8) | d[5]) != 1) return DnsStatus::kMismatch;
+        std::string qname;
+        if (!read_name(d, len, 12, &qname)) return DnsStatus::kMismatch;
+        const size_t after = skip_name(d, len, 12);
+        if (after == 0 || after + 4 > len) return DnsStatus::kMismatch;
+        std::string want = *asked_name;
+        while (!want.empty() && want.back() == '.') want.pop_back();
+        for (char& ch : want) {
+            if (ch >= 'A' && ch <= 'Z') ch = static_cast<char>(ch + 32);
+        }
+        if (qname != want) return DnsStatus::kMismatch;
+        if (((d[after] << 8) | d[after + 1]) != qtype || ((d[after + 2] << 8) | d[after + 3]) != 1) return DnsStatus::kMismatch;
+    }
     if (d[2] & 0x02) {
         if (truncated) *truncated = true;
     }
@@ -346,8 +365,8 @@ int remaining_ms(int64_t deadline_ns, int cap_ms) {
 
 // One query/response exchange over UDP (or TCP when `tcp`). Returns kTimeout when nothing usable
 // arrived in time.
-DnsStatus exchange(const ServerAddr& server, const std::vector<uint8_t>& query, uint16_t id, uint16_t qtype, bool tcp,
-                   int timeout_ms, IpAddress* out, bool* truncated) {
+DnsStatus exchange(const ServerAddr& server, const std::string& name, const std::vector<uint8_t>& query, uint16_t id,
+                   uint16_t qtype, bool tcp, int timeout_ms, IpAddress* out, bool* truncated) {
     const int fd = socket(server.family, (tcp ? SOCK_STREAM : SOCK_DGRAM) | SOCK_CLOEXEC | SOCK_NONBLOCK, 0);
     if (fd < 0) return DnsStatus::kError;
     DnsStatus result = DnsStatus::kTimeout;
@@ -392,9 +411,10 @@ DnsStatus exchange(const ServerAddr& server, const std::vector<uint8_t>& query, 
                 break;
             }
             if (!tcp) {
-                const DnsStatus st = dns_parse_response(buf, static_cast<size_t>(n), id, out, truncated, qtype);
-                if (st == DnsStatus::kError && static_cast<size_t>(n) >= 2 &&
-                    static_cast<uint16_t>((buf[0] << 8) | buf[1]) != id) {
+                const DnsStatus st = dns_parse_response(buf, static_cast<size_t>(n), id, out, truncated, qtype, &name);
+                if (st == DnsStatus::kMismatch || (st == DnsStatus::kError && static_cast<size_t>(n) >= 2 &&
+                                                   static_cast<uint16_t>((buf[0] << 8) | buf[1]) != id)) {
+                    if (truncated) *truncated = false;
                     continue;  // a stray datagram for some other query: keep waiting
                 }
                 result = st;
@@ -408,7 +428,8 @@ DnsStatus exchange(const ServerAddr& server, const std::vector<uint8_t>& query, 
                 break;
             }
             if (have < msg_len + 2) continue;
-            result = dns_parse_response(buf + 2, msg_len, id, out, nullptr, qtype);
+            result = dns_parse_response(buf + 2, msg_len, id, out, nullptr, qtype, &name);
+            if (result == DnsStatus::kMismatch) result = DnsStatus::kError;
             break;
         }
     } while (false);
@@ -456,10 +477,10 @@ DnsStatus resolve_address(const std::string& host, const DnsConfig& cfg, IpAddre
                     const int timeout_ms = remaining_ms(deadline_ns, cfg.timeout_ms);
                     if (timeout_ms <= 0) return DnsStatus::kTimeout;
                     bool truncated = false;
-                    DnsStatus st = exchange(server, query, id, qtype, false, timeout_ms, out, &truncated);
+                    DnsStatus st = exchange(server, name, query, id, qtype, false, timeout_ms, out, &truncated);
                     if (truncated && st != DnsStatus::kOk) {
                         const int t2 = remaining_ms(deadline_ns, cfg.timeout_ms);
-                        if (t2 > 0) st = exchange(server, query, id, qtype, true, t2, out, nullptr);
+                        if (t2 > 0) st = exchange(server, name, query, id, qtype, true, t2, out, nullptr);
                     }
                     if (st == DnsStatus::kOk) return DnsStatus::kOk;
                     if (st == DnsStatus::kNotFound || st == DnsStatus::kNoData) {

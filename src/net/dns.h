@@ -55,7 +55,8 @@ struct DnsConfig {
 
 // kNotFound: the name does not exist (NXDOMAIN). kNoData: it exists but has no record of the
 // type asked for (worth asking again for the other address family).
-enum class DnsStatus { kOk, kNotFound, kNoData, kTimeout, kError };
+// kMismatch: the message does not repeat the question that was asked (see dns_parse_response).
+enum class DnsStatus { kOk, kNotFound, kNoData, kTimeout, kError, kMismatch };
 
 constexpr uint16_t kDnsTypeA = 1;
 constexpr uint16_t kDnsTypeAAAA = 28;
@@ -70,8 +71,11 @@ std::vector<std::string> dns_candidates(const std::string& host, const DnsConfig
 bool dns_build_query(const std::string& name, uint16_t id, std::vector<uint8_t>* out, uint16_t qtype = kDnsTypeA);
 // Parses a response to query `id`. kOk sets *out to the first record of type `qtype` for the
 // queried name, following CNAMEs inside the message. *truncated is set when the TC bit is on.
+// With `asked_name` the question section must be exactly that question (one entry, same name
+// ignoring case, type `qtype`, class IN); otherwise the result is kMismatch and the caller should
+// treat the message as a stray datagram.
 DnsStatus dns_parse_response(const uint8_t* data, size_t len, uint16_t id, IpAddress* out, bool* truncated,
-                             uint16_t qtype = kDnsTypeA);
+                             uint16_t qtype = kDnsTypeA, const std::string* asked_name = nullptr);
 
 // Full blocking lookup: literal, "localhost", hosts file, then DNS (A first; AAAA when the name
 // has no A record). `deadline_ms` bounds the whole operation (0: only the per-try timeouts apply).

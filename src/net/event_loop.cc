@@ -173,11 +173,16 @@ void EventLoop::run() {
         }
         if (woken) drain_mailbox();
         run_timers();
-        if (!deferred_.empty()) {
-            std::vector<std::function<void()>> batch;
-            batch.swap(deferred_);
-            for (auto& fn : batch) fn();
-        }
+        run_deferred();
+    }
+    run_deferred();  // left by an early exit from the loop
+}
+
+void EventLoop::run_deferred() {
+    while (!deferred_.empty()) {
+        std::vector<std::function<void()>> batch;
+        batch.swap(deferred_);
+        for (auto& fn : batch) fn();
     }
 }
 

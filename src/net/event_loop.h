@@ -86,6 +86,7 @@ class EventLoop {
 
     void drain_mailbox();
     void run_timers();
+    void run_deferred();
     int next_timeout_ms() const;
 
     int epfd_ = -1;

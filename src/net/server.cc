@@ -86,6 +86,10 @@ void Connection::close_now() {
     worker_->release(this);
 }
 
+bool Connection::input_full() const {
+    return in_pos_ == 0 && in_len_ == in_cap_ && in_cap_ >= worker_->options().max_header_bytes + kInitialInputCapacity;
+}
+
 void Connection::update_interest() {
     if (fd_ < 0) return;
     uint32_t ev = EPOLLRDHUP;
@@ -95,6 +99,10 @@ void Connection::update_interest() {
     if (peer_closed_) can_read = false;
     if (can_read) ev |= EPOLLIN;
     if (peer_closed_) ev &= ~static_cast<uint32_t>(EPOLLRDHUP);
+    // Nothing more can be taken in until the pending request is answered: with a level-triggered
+    // loop neither "readable" nor "peer half-closed" may stay armed, or the loop spins on an event
+    // it cannot consume. EPOLLHUP/EPOLLERR are always reported, so a dead peer is still noticed.
+    if (!streaming_ && input_full()) ev &= ~static_cast<uint32_t>(EPOLLIN | EPOLLRDHUP);
     if (ev == registered_events_) return;
     registered_events_ = ev;
     worker_->loop().modify(fd_, ev, this);
@@ -118,6 +126,9 @@ void Connection::on_events(uint32_t events) {
     last_active_ns_ = worker_->loop().now_ns();
     const size_t max_cap = worker_->options().max_header_bytes + kInitialInputCapacity;
     while (fd_ >= 0) {
+        // A metrics stream has no use for further input: whatever the client sends after the
+        // request is read and dropped, so that the socket never stays readable.
+        if (streaming_) in_len_ = in_pos_ = 0;
         if (in_len_ == in_cap_) {
             if (in_pos_ > 0) {
                 std::memmove(in_.get(), in_.get() + in_pos_, in_len_ - in_pos_);
@@ -138,8 +149,10 @@ void Connection::on_events(uint32_t events) {
         const size_t space = in_cap_ - in_len_;
         const ssize_t n = recv(fd_, in_.get() + in_len_, space, 0);
         if (n > 0) {
-            in_len_ += static_cast<size_t>(n);
-            process_input();
+            if (!streaming_) {
+                in_len_ += static_cast<size_t>(n);
+                process_input();
+            }
             if (static_cast<size_t>(n) < space) break;  // socket drained
             if (want_write_ && !streaming_) break;      // peer is not reading: stop producing for it
             continue;
@@ -376,7 +389,18 @@ void Worker::adopt(int fd) {
 }
 
 void Worker::release(Connection* c) {
-    free_.push_back(c->index_);
+    // The slot becomes reusable only at the end of this loop iteration: the batch of epoll events
+    // being dispatched may still hold an event for the descriptor that was just closed, and its
+    // handler pointer is this object. Reused at once, the object would receive a stale EPOLLERR
+    // or EPOLLIN that belongs to the previous connection (HttpClient::retire defers for the same
+    // reason).
+    parked_.push_back(c->index_);
+    if (parked_.size() == 1) {
+        loop_.defer([this] {
+            free_.insert(free_.end(), parked_.begin(), parked_.end());
+            parked_.clear();
+        });
+    }
     --open_count_;
     stats_.connections_open.fetch_sub(1, std::memory_order_relaxed);
     if (draining_ && open_count_ == 0) loop_.stop();

@@ -80,6 +80,7 @@ class Connection final : public EventHandler {
     void flush();
     void update_interest();
     bool discard_body_bytes();
+    bool input_full() const;  // buffer at its limit with nothing consumable (a deferred request and a greedy pipeliner)
 
     Worker* worker_;
     const uint32_t index_;
@@ -187,6 +188,7 @@ class Worker final : public EventHandler {
     bool draining_ = false;
     std::vector<std::unique_ptr<Connection>> conns_;
     std::vector<uint32_t> free_;
+    std::vector<uint32_t> parked_;  // closed in this loop iteration; joins free_ when the iteration ends
     size_t open_count_ = 0;
     std::vector<Worker*>* peers_ = nullptr;  // round-robin mode: all workers
     size_t rr_next_ = 0;

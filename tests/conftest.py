@@ -51,10 +51,20 @@ def pytest_addoption(parser):
                           "(asan: AddressSanitizer+UBSan, tsan: ThreadSanitizer; SURVEY.md 5.2)")
 
 
+_deselected = {"count": 0}
+
+
+def pytest_deselected(items):
+    _deselected["count"] += len(items)
+
+
 def pytest_sessionfinish(session, exitstatus):
-    # `-m gpu` deselects everything by design; do not let that read as a failure.
+    # `-m gpu` deselects everything by design; do not let that read as a failure. Only a selection
+    # that really was "all tests collected, every one of them deselected" qualifies: a session that
+    # collected nothing at all (an import error, a wrong path) keeps pytest's error code.
     markexpr = getattr(session.config.option, "markexpr", "") or ""
-    if exitstatus == pytest.ExitCode.NO_TESTS_COLLECTED and markexpr.strip() == "gpu":
+    collected_fine = _deselected["count"] >= 100 and not getattr(session, "shouldfail", False)
+    if exitstatus == pytest.ExitCode.NO_TESTS_COLLECTED and markexpr.strip() == "gpu" and collected_fine:
         tr = session.config.pluginmanager.get_plugin("terminalreporter")
         if tr is not None:
             tr.write_line("no GPU tests exist: the project is CPU-only (SURVEY.md 2.3); an empty `-m gpu` selection is expected")

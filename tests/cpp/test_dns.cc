@@ -139,6 +139,17 @@ TEST(dns_response_parsing) {
     r = response(8, "aloha.test", 0,
                  {record(kPointerToQuestion, 5, encode_name("real.test")), record(encode_name("real.test"), 1, {192, 0, 2, 9})});
     for (size_t n = 0; n < r.size(); ++n) dns_parse_response(r.data(), n, 8, &ip, nullptr);
+    // The question must be the one that was asked: same name (any case), same type, exactly one.
+    r = response(15, "aloha.test", 0, {record(kPointerToQuestion, 1, {10, 1, 2, 3})});
+    const std::string asked = "ALOHA.test.", other = "evil.test";
+    CHECK(dns_parse_response(r.data(), r.size(), 15, &ip, nullptr, kDnsTypeA, &asked) == DnsStatus::kOk);
+    CHECK(dns_parse_response(r.data(), r.size(), 15, &ip, nullptr, kDnsTypeA, &other) == DnsStatus::kMismatch);
+    CHECK(dns_parse_response(r.data(), r.size(), 15, &ip, nullptr, kDnsTypeAAAA, &asked) == DnsStatus::kMismatch);
+    r = response(15, "evil.test", 3, {});  // somebody else's NXDOMAIN is not ours
+    CHECK(dns_parse_response(r.data(), r.size(), 15, &ip, nullptr, kDnsTypeA, &asked) == DnsStatus::kMismatch);
+    r = response(15, "aloha.test", 0, {});
+    r[5] = 0;  // QDCOUNT 0: nothing says what this answers
+    CHECK(dns_parse_response(r.data(), r.size(), 15, &ip, nullptr, kDnsTypeA, &asked) == DnsStatus::kMismatch);
     // A compression loop terminates.
     std::vector<uint8_t> loop = response(14, "aloha.test", 0, {});
     loop[7] = 1;

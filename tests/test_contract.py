@@ -236,6 +236,19 @@ def test_webjars_directory(hola_server, tmp_path):
     assert get(srv, "/webjars/../secret.txt").status == 404
     assert get(srv, "/webjars/%2e%2e/secret.txt").status == 404
     assert get(srv, "/webjars/swagger-ui/2.1.4/..%2f..%2f..%2fsecret.txt").status == 404
+    # A symbolic link inside the directory must not lead out of it; one that stays inside is fine.
+    (ui / "link.txt").symlink_to(tmp_path / "secret.txt")
+    (ui / "alias.js").symlink_to(ui / "swagger-ui.js")
+    (root / "up").symlink_to(tmp_path)
+    assert get(srv, "/webjars/swagger-ui/2.1.4/link.txt").status == 404
+    assert get(srv, "/webjars/up/secret.txt").status == 404
+    assert get(srv, "/webjars/swagger-ui/2.1.4/alias.js").body == b"var x = 1;"
+    # Served from memory, but a changed file is noticed (size or mtime).
+    assert get(srv, "/webjars/swagger-ui/2.1.4/swagger-ui.js").body == b"var x = 1;"
+    (ui / "swagger-ui.js").write_text("var x = 22;")
+    assert get(srv, "/webjars/swagger-ui/2.1.4/swagger-ui.js").body == b"var x = 22;"
+    r = client.get("127.0.0.1", srv.port, "/webjars/swagger-ui/2.1.4/swagger-ui.js", method="HEAD")
+    assert r.status == 200 and r.header("Content-Length") == "11"
     # Without --webjars-dir the Swagger-UI assets are absent (they are not on the build box either),
     # but the page the landing page frames is replaced by a built-in API browser, so "/" works.
     bare = hola_server()

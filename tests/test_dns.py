@@ -95,6 +95,16 @@ def test_slow_dns_is_cut_off_by_the_command_timeout(hola_server, fake_aloha, fak
     assert time.time() - t0 < 3  # a lookup stuck on a dead name server does not hold up shutdown
 
 
+def test_answer_to_a_different_question_is_ignored(hola_server, fake_aloha, fake_dns, tmp_path):
+    """A datagram with the right id but another question section (a spoofing attempt, or a late
+    answer to an earlier query) is not the answer: the resolver keeps waiting for the real one."""
+    dns = fake_dns({"aloha.msa.svc.cluster.local": "127.0.0.1"})
+    dns.stray_first = ("evil.example", "127.0.0.9")  # nothing listens there: taking it would mean the fallback
+    srv = hola_server(args=["--aloha-url", "http://aloha:%d/" % fake_aloha.port, "--feign-max-attempts", "1"],
+                      env=dns_env(tmp_path, dns))
+    assert chain(srv) == ["Hola de unknown"] + fake_aloha.payload
+
+
 def test_hosts_file_beats_dns(hola_server, fake_aloha, fake_dns, tmp_path):
     dns = fake_dns({})
     env = dns_env(tmp_path, dns)

@@ -282,3 +282,89 @@ def test_descriptor_exhaustion_does_not_spin_or_die(hola_server, native_build):
     ru = resource.getrusage(resource.RUSAGE_CHILDREN)
     burnt = (ru.ru_utime + ru.ru_stime) - (ru_before.ru_utime + ru_before.ru_stime)
     assert burnt < 0.5, burnt  # a spinning accept loop would have burnt ~1 s of CPU
+
+
+# -- regressions from the round-1 review ---------------------------------------------------------
+
+def _cpu_seconds(pid: int) -> float:
+    import os
+    fields = open("/proc/%d/stat" % pid).read().rsplit(")", 1)[1].split()
+    return (int(fields[11]) + int(fields[12])) / os.sysconf("SC_CLK_TCK")  # utime + stime
+
+
+def test_stream_client_sending_garbage_does_not_pin_a_worker(hola_server):
+    """A metrics-stream client that keeps writing used to leave the socket readable for ever:
+    level-triggered epoll then spun one worker at 100 % CPU. The input is now read and dropped."""
+    srv = hola_server(threads=1)
+    c = client.Connection("127.0.0.1", srv.port)
+    c.send_raw(client.build_request("GET", "/hystrix.stream?delay=100"))
+    while b"\r\n\r\n" not in c.buf:
+        assert c._fill()
+    c.send_raw(b"x" * 80 * 1024)
+    time.sleep(0.3)
+    before = _cpu_seconds(srv.proc.pid)
+    time.sleep(1.5)
+    used = _cpu_seconds(srv.proc.pid) - before
+    assert used < 0.3, "worker burned %.2f s of CPU in 1.5 s" % used
+    # The stream is still alive and the worker still serves others.
+    assert client.get("127.0.0.1", srv.port, "/api/hola").body == HOLA
+    c.sock.settimeout(2)
+    assert c.sock.recv(65536)
+    c.close()
+
+
+def test_deferred_request_with_full_buffer_and_half_closed_peer_does_not_spin(hola_server, fake_aloha):
+    """While the downstream call of /api/hola-chaining is in flight the connection stops parsing.
+    A client that pipelines more than the buffer holds and then half-closes used to leave
+    EPOLLRDHUP armed on a socket whose EOF could not be read: a busy loop until the call settled.
+    Every pipelined request must still be answered, in order."""
+    fake_aloha.delay = 1.5
+    srv = hola_server(args=["--aloha-url", fake_aloha.url, "--max-header-bytes", "1024",
+                            "-Dhystrix.command.default.execution.isolation.thread.timeoutInMilliseconds=5000"], threads=1)
+    c = client.Connection("127.0.0.1", srv.port, timeout=10)
+    extra = 400  # ~16 KB of pipelined requests against a 5 KB buffer
+    c.send_raw(client.build_request("GET", "/api/hola-chaining") + client.build_request("GET", "/api/hola") * extra)
+    c.sock.shutdown(socket.SHUT_WR)
+    time.sleep(0.3)
+    before = _cpu_seconds(srv.proc.pid)
+    time.sleep(0.9)
+    used = _cpu_seconds(srv.proc.pid) - before
+    assert used < 0.2, "worker burned %.2f s of CPU in 0.9 s while the call was pending" % used
+    first = c.read_response()
+    assert first.status == 200 and first.body.startswith(b'["Hola de unknown","Aloha mai')
+    for _ in range(extra):
+        assert c.read_response().body == HOLA
+    assert c.closed_by_peer()
+    c.close()
+
+
+def test_connection_slot_is_not_reused_within_one_batch_of_events(hola_server, fake_aloha):
+    """One worker, stopped with SIGSTOP while three things queue up in this order: the downstream
+    reply for deferred connection A, a new client B, and a reset of A. On resume the reply cannot
+    be written to A (its slot is freed), B is accepted, and A's reset is delivered last. B must be
+    answered: the freed slot may not be handed to B while A's stale event is still in the batch."""
+    import os
+    import signal
+    import struct
+    fake_aloha.delay = 0.4
+    for _ in range(3):  # the order of readiness is the kernel's; repeat to be sure the window was hit
+        srv = hola_server(args=["--aloha-url", fake_aloha.url], threads=1)
+        a = client.Connection("127.0.0.1", srv.port)
+        a.send_raw(client.build_request("GET", "/api/hola-chaining"))
+        time.sleep(0.15)  # the downstream call is in flight
+        os.kill(srv.proc.pid, signal.SIGSTOP)
+        try:
+            time.sleep(0.5)  # the downstream reply has arrived at the stopped process
+            b = client.Connection("127.0.0.1", srv.port)
+            b.send_raw(client.build_request("GET", "/api/hola"))
+            time.sleep(0.05)
+            a.sock.setsockopt(socket.SOL_SOCKET, socket.SO_LINGER, struct.pack("ii", 1, 0))
+            a.sock.close()  # RST
+            time.sleep(0.05)
+        finally:
+            os.kill(srv.proc.pid, signal.SIGCONT)
+        r = b.read_response()
+        assert r.status == 200 and r.body == HOLA
+        assert b.request("GET", "/api/health").body == b"I'm ok"
+        b.close()
+        srv.stop()
