@@ -74,6 +74,7 @@ def _declare(L: ctypes.CDLL) -> None:
     L.hola_service_threads.argtypes = [c_void_p]
     L.hola_service_stats.argtypes = [c_void_p, POINTER(c_uint64), POINTER(c_uint64)]
     L.hola_service_trace_stats.argtypes = [c_void_p, POINTER(c_uint64), POINTER(c_uint64)]
+    L.hola_service_stats_json.argtypes = [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]
     L.hola_service_stop.argtypes = [c_void_p]
 
 
@@ -342,6 +343,12 @@ class Service:
         rep, drop = c_uint64(), c_uint64()
         lib().hola_service_trace_stats(self._h, byref(rep), byref(drop))
         return {"reported": rep.value, "dropped": drop.value}
+
+    def stats_json(self) -> Dict:
+        """Totals, CPU seconds, span counts and one entry per worker thread (see include/hola.h)."""
+        import json
+        _, data = _call_out(lib().hola_service_stats_json, self._h)
+        return json.loads(data)
 
     def __enter__(self) -> "Service":
         return self.start()

@@ -111,6 +111,22 @@ class HolaServer:
     def __exit__(self, *exc) -> None:
         self.stop()
 
+    def stats(self, timeout: float = 5.0) -> Dict:
+        """Asks the running process for its counters (SIGUSR1 -> one ``hola-stats {json}`` line on
+        stderr): totals, CPU seconds, span counts and one entry per worker thread."""
+        import json
+        if self.proc is None or self.proc.poll() is not None:
+            raise RuntimeError("hola is not running")
+        seen = sum(1 for line in self.stderr_lines if line.startswith("hola-stats "))
+        self.proc.send_signal(signal.SIGUSR1)
+        deadline = time.monotonic() + timeout
+        while time.monotonic() < deadline:
+            lines = [line for line in self.stderr_lines if line.startswith("hola-stats ")]
+            if len(lines) > seen:
+                return json.loads(lines[-1][len("hola-stats "):])
+            time.sleep(0.005)
+        raise RuntimeError("no hola-stats line within %.1f s" % timeout)
+
     # -- conveniences ------------------------------------------------------------------------
     @property
     def base_url(self) -> str:

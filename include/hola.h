@@ -130,6 +130,12 @@ int hola_service_threads(const hola_service* s);
 void hola_service_stats(const hola_service* s, uint64_t* requests, uint64_t* connections);
 /* spans accepted by the collector / spans dropped so far. */
 void hola_service_trace_stats(const hola_service* s, uint64_t* reported, uint64_t* dropped);
+/* All counters as one JSON object: totals, process CPU seconds, span counts, the accept mode and
+ * one entry per worker thread {id, requests, connections, connections_open, cpu_s} - the place to
+ * see whether connections are spread evenly over the threads (the reference relies on Undertow's
+ * acceptor dealing them in turn, /root/reference/pom.xml:122-129). The `hola` executable prints
+ * the same object as "hola-stats {...}" on stderr when it receives SIGUSR1. */
+int hola_service_stats_json(const hola_service* s, char** out, size_t* out_len);
 void hola_service_stop(hola_service* s);
 
 #ifdef __cplusplus

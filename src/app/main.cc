@@ -46,6 +46,7 @@ int main(int argc, char** argv) {
     sigemptyset(&sigs);
     sigaddset(&sigs, SIGINT);
     sigaddset(&sigs, SIGTERM);
+    sigaddset(&sigs, SIGUSR1);  // dump counters (Service::stats_json) and carry on
     pthread_sigmask(SIG_BLOCK, &sigs, nullptr);
     signal(SIGPIPE, SIG_IGN);
 
@@ -56,7 +57,10 @@ int main(int argc, char** argv) {
         return 1;
     }
     int sig = 0;
-    sigwait(&sigs, &sig);
+    while (sigwait(&sigs, &sig) == 0 && sig == SIGUSR1) {
+        std::fprintf(stderr, "hola-stats %s\n", service.stats_json().c_str());
+        std::fflush(stderr);
+    }
     if (!service.config().quiet) std::fprintf(stderr, "hola: signal %d, shutting down\n", sig);
     service.stop();
     return 0;

@@ -31,7 +31,9 @@ std::string usage_text() {
            "                              on IPv6 and IPv4)\n"
            "  --threads N                 event-loop threads (default: one per available CPU, capped by the cgroup CPU quota)\n"
            "  --cpus LIST                 pin thread i to the i-th CPU of LIST (e.g. 0,1,2,3 or 0-3)\n"
-           "  --accept-mode MODE          reuseport (default; one listener per thread) | rr (one acceptor, round-robin)\n"
+           "  --accept-mode MODE          balanced (default: a listener per thread, new connections go to the least-loaded\n"
+           "                              thread) | reuseport (a listener per thread, the kernel's hash decides) |\n"
+           "                              rr (one acceptor deals connections in turn; no SO_REUSEPORT)\n"
            "  --aloha-url URL             downstream base URL (default http://aloha:8080/)\n"
            "  --feign-max-attempts N      tries per downstream call on connection failures (default 5, as Feign's\n"
            "                              default Retryer: pauses of 150, 225, 337, 506 ms; 1 disables retrying)\n"
@@ -111,8 +113,8 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
         } else if (a == "--cpus") {
             if (!value(&v) || !parse_cpu_list(v, &cfg->server.cpu_affinity)) return fail("bad --cpus list");
         } else if (a == "--accept-mode") {
-            if (!value(&v) || (v != "reuseport" && v != "rr")) return fail("--accept-mode is reuseport or rr");
-            cfg->server.reuse_port = v == "reuseport";
+            if (!value(&v) || (v != "balanced" && v != "reuseport" && v != "rr")) return fail("--accept-mode is balanced, reuseport or rr");
+            cfg->server.accept_mode = v == "balanced" ? AcceptMode::kBalanced : v == "reuseport" ? AcceptMode::kReusePort : AcceptMode::kRoundRobin;
         } else if (a == "--aloha-url") {
             std::string host, path;
             uint16_t port = 80;
@@ -295,6 +297,40 @@ bool Service::start(std::string* error) {
     return true;
 }
 
+std::string Service::stats_json() const {
+    if (!server_) return "{}";
+    rusage ru{};
+    getrusage(RUSAGE_SELF, &ru);
+    const ServerStats st = server_->stats();
+    const TracerStats ts = tracer_->stats();
+    const char* mode = config_.server.accept_mode == AcceptMode::kBalanced    ? "balanced"
+                       : config_.server.accept_mode == AcceptMode::kReusePort ? "reuseport"
+                                                                              : "rr";
+    char buf[512];
+    std::snprintf(buf, sizeof buf,
+                  "{\"requests\":%llu,\"bad_requests\":%llu,\"connections_accepted\":%llu,\"connections_open\":%llu,"
+                  "\"cpu_user_s\":%.6f,\"cpu_sys_s\":%.6f,\"accept_mode\":\"%s\",\"threads\":%d,"
+                  "\"spans\":{\"reported\":%llu,\"dropped\":%llu,\"posts_ok\":%llu,\"posts_failed\":%llu},\"workers\":[",
+                  static_cast<unsigned long long>(st.requests), static_cast<unsigned long long>(st.bad_requests),
+                  static_cast<unsigned long long>(st.connections_accepted), static_cast<unsigned long long>(st.connections_open),
+                  static_cast<double>(ru.ru_utime.tv_sec) + static_cast<double>(ru.ru_utime.tv_usec) / 1e6,
+                  static_cast<double>(ru.ru_stime.tv_sec) + static_cast<double>(ru.ru_stime.tv_usec) / 1e6, mode, server_->threads(),
+                  static_cast<unsigned long long>(ts.spans_reported), static_cast<unsigned long long>(ts.spans_dropped),
+                  static_cast<unsigned long long>(ts.posts_ok), static_cast<unsigned long long>(ts.posts_failed));
+    std::string out = buf;
+    bool first = true;
+    for (const WorkerSnapshot& w : server_->worker_stats()) {
+        std::snprintf(buf, sizeof buf, "%s{\"id\":%d,\"requests\":%llu,\"connections\":%llu,\"connections_open\":%llu,\"cpu_s\":%.6f}",
+                      first ? "" : ",", w.id, static_cast<unsigned long long>(w.requests),
+                      static_cast<unsigned long long>(w.connections_accepted), static_cast<unsigned long long>(w.connections_open),
+                      w.cpu_seconds);
+        out.append(buf);
+        first = false;
+    }
+    out.append("]}");
+    return out;
+}
+
 void Service::stop() {
     if (!started_) return;
     started_ = false;
@@ -302,8 +338,8 @@ void Service::stop() {
     dns_->shutdown();
     tracer_->stop();
     if (config_.app.verbose) {
-        // A cheap profile for the record: how the process spent its CPU and how well the event
-        // loops batched their work.
+        // A cheap profile for the record: how the process spent its CPU, how well the event
+        // loops batched their work, and how evenly the workers shared it.
         rusage ru{};
         getrusage(RUSAGE_SELF, &ru);
         const ServerStats st = server_->stats();
@@ -321,6 +357,14 @@ void Service::stop() {
                       static_cast<unsigned long long>(st.loop_blocking_waits), static_cast<unsigned long long>(ts.spans_reported),
                       static_cast<unsigned long long>(ts.spans_dropped), ru.ru_nvcsw, ru.ru_nivcsw);
         log("INFO", msg);
+        std::string per_worker = "workers (requests/connections/cpu_s):";
+        for (const WorkerSnapshot& w : server_->worker_stats()) {
+            char item[96];
+            std::snprintf(item, sizeof item, " %d=%llu/%llu/%.2f", w.id, static_cast<unsigned long long>(w.requests),
+                          static_cast<unsigned long long>(w.connections_accepted), w.cpu_seconds);
+            per_worker.append(item);
+        }
+        log("INFO", per_worker);
     }
 }
 

@@ -66,6 +66,10 @@ class Service {
     bool tracing() const { return tracer_ && tracer_->enabled(); }
     ServerStats server_stats() const { return server_->stats(); }
     TracerStats tracer_stats() const { return tracer_->stats(); }
+    // Counters as one JSON object: totals, process CPU time, span counts and one entry per worker
+    // (requests, connections, CPU seconds). Printed on SIGUSR1 by the executable (`hola-stats {...}`
+    // on stderr) and available through the C ABI; safe to call while the service runs.
+    std::string stats_json() const;
     HolaApp& app() { return *app_; }
     const ServiceConfig& config() const { return config_; }
 

@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 
 namespace hola {
 
@@ -323,7 +324,7 @@ bool Worker::open_listener(std::string* error) {
     const int one = 1;
     const int zero = 0;
     setsockopt(fd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
-    if (options_.reuse_port) setsockopt(fd, SOL_SOCKET, SO_REUSEPORT, &one, sizeof one);
+    if (options_.accept_mode != AcceptMode::kRoundRobin) setsockopt(fd, SOL_SOCKET, SO_REUSEPORT, &one, sizeof one);
     if (v6) setsockopt(fd, IPPROTO_IPV6, IPV6_V6ONLY, &zero, sizeof zero);
     if (bind(fd, reinterpret_cast<sockaddr*>(&storage), addr_len) != 0) {
         *error = "bind " + options_.bind_address + ":" + std::to_string(options_.port) + ": " + std::strerror(errno);
@@ -358,20 +359,44 @@ void Worker::on_events(uint32_t /*events*/) {
             return;
         }
         set_nodelay(fd);
+        Worker* target = this;
         if (peers_ && peers_->size() > 1) {
-            Worker* target = (*peers_)[rr_next_++ % peers_->size()];
-            if (target != this) {
-                target->loop().post([target, fd] { target->adopt(fd); });
-                continue;
-            }
+            target = options_.accept_mode == AcceptMode::kRoundRobin ? (*peers_)[rr_next_++ % peers_->size()] : least_loaded();
         }
-        adopt(fd);
+        // Counted at the moment of the decision, not when the target gets round to adopting it:
+        // several acceptors deciding at the same time must see each other's choices.
+        target->stats_.connections_open.fetch_add(1, std::memory_order_relaxed);
+        if (target != this) {
+            target->loop().post([target, fd] { target->adopt(fd); });
+        } else {
+            adopt(fd);
+        }
     }
+}
+
+// The worker a new connection should go to: this one if no other has fewer open connections,
+// else the least loaded (scanning from the next id on, so that ties do not all go to worker 0).
+Worker* Worker::least_loaded() {
+    const std::vector<Worker*>& all = *peers_;
+    const uint64_t mine = stats_.connections_open.load(std::memory_order_relaxed);
+    Worker* best = this;
+    uint64_t best_load = mine;
+    const size_t n = all.size();
+    for (size_t k = 1; k < n; ++k) {
+        Worker* w = all[(static_cast<size_t>(id_) + k) % n];
+        const uint64_t load = w->stats_.connections_open.load(std::memory_order_relaxed);
+        if (load < best_load) {
+            best = w;
+            best_load = load;
+        }
+    }
+    return best;
 }
 
 void Worker::adopt(int fd) {
     if (draining_) {
         close(fd);
+        stats_.connections_open.fetch_sub(1, std::memory_order_relaxed);
         return;
     }
     Connection* c;
@@ -384,7 +409,6 @@ void Worker::adopt(int fd) {
     }
     ++open_count_;
     stats_.connections_accepted.fetch_add(1, std::memory_order_relaxed);
-    stats_.connections_open.fetch_add(1, std::memory_order_relaxed);
     c->start(fd);
 }
 
@@ -517,6 +541,9 @@ void Worker::thread_main() {
         }
     }
     app_->on_worker_exit(*this);
+    timespec ts;
+    if (clock_gettime(CLOCK_THREAD_CPUTIME_ID, &ts) == 0)
+        cpu_seconds_.store(static_cast<double>(ts.tv_sec) + static_cast<double>(ts.tv_nsec) / 1e9, std::memory_order_relaxed);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -570,7 +597,7 @@ bool Server::start(std::string* error) {
     }
     for (int i = 0; i < n; ++i) {
         Worker& w = *workers_[static_cast<size_t>(i)];
-        if (!options_.reuse_port && i > 0) break;  // single acceptor
+        if (options_.accept_mode == AcceptMode::kRoundRobin && i > 0) break;  // single acceptor
         if (!w.open_listener(error)) {
             workers_.clear();
             worker_ptrs_.clear();
@@ -585,7 +612,11 @@ bool Server::start(std::string* error) {
             options_.port = bound_port_;  // later listeners join the same (possibly ephemeral) port
         }
     }
-    if (!options_.reuse_port) workers_[0]->peers_ = &worker_ptrs_;
+    if (options_.accept_mode == AcceptMode::kRoundRobin) {
+        workers_[0]->peers_ = &worker_ptrs_;
+    } else if (options_.accept_mode == AcceptMode::kBalanced) {
+        for (auto& w : workers_) w->peers_ = &worker_ptrs_;
+    }
     for (auto& w : workers_) {
         Worker* wp = w.get();
         wp->thread_ = std::thread([wp] { wp->thread_main(); });
@@ -620,6 +651,26 @@ ServerStats Server::stats() const {
         }
     }
     return s;
+}
+
+std::vector<WorkerSnapshot> Server::worker_stats() const {
+    std::vector<WorkerSnapshot> out;
+    for (const auto& w : workers_) {
+        WorkerSnapshot s;
+        s.id = w->id_;
+        s.connections_accepted = w->stats_.connections_accepted.load(std::memory_order_relaxed);
+        s.connections_open = w->stats_.connections_open.load(std::memory_order_relaxed);
+        s.requests = w->stats_.requests.load(std::memory_order_relaxed);
+        s.cpu_seconds = w->cpu_seconds_.load(std::memory_order_relaxed);
+        if (started_ && w->thread_.joinable()) {
+            clockid_t clock;
+            timespec ts;
+            if (pthread_getcpuclockid(w->thread_.native_handle(), &clock) == 0 && clock_gettime(clock, &ts) == 0)
+                s.cpu_seconds = static_cast<double>(ts.tv_sec) + static_cast<double>(ts.tv_nsec) / 1e9;
+        }
+        out.push_back(s);
+    }
+    return out;
 }
 
 }  // namespace hola

@@ -4,6 +4,15 @@
 // Replaces the Undertow listener the reference gets from WildFly Swarm on :8080
 // (/root/reference/Readme.md:16, /root/reference/Dockerfile:8, /root/reference/pom.xml:74).
 //
+// Connection placement (AcceptMode). Undertow's acceptor deals new connections to its I/O threads
+// in turn (/root/reference/pom.xml:122-129 pulls it in), so a handful of keep-alive clients ends
+// up spread evenly. Plain SO_REUSEPORT does not: the kernel picks the listener by a hash of the
+// connection's addresses, and 64 connections over 16 listeners land anywhere between one and eight
+// per worker - in a closed loop the worker with eight saturates while the worker with one idles.
+// The default mode therefore keeps one listener per worker (accepting stays parallel, a second
+// process can still join the port for a rolling restart) but lets the accepting worker pass a new
+// connection to the least-loaded worker when it is not itself among the least loaded.
+//
 // Request life cycle on a worker thread:
 //   recv -> parse_request_head (zero copy) -> Application::handle -> bytes appended to the
 //   connection's output buffer -> one send() per batch of pipelined requests.
@@ -107,13 +116,19 @@ class Connection final : public EventHandler {
     int64_t last_active_ns_ = 0;
 };
 
+enum class AcceptMode : uint8_t {
+    kBalanced,    // a listener per worker + hand-off to the least-loaded worker (default)
+    kReusePort,   // a listener per worker, the kernel's hash decides (no hand-off)
+    kRoundRobin,  // worker 0 accepts and deals connections in turn; no SO_REUSEPORT
+};
+
 struct ServerOptions {
     std::string bind_address = "0.0.0.0";
     uint16_t port = 8080;
     int threads = 0;                  // 0: one per available CPU
     int backlog = 1024;
     size_t max_header_bytes = 65536;  // request line + headers
-    bool reuse_port = true;           // false: worker 0 accepts and deals connections round-robin
+    AcceptMode accept_mode = AcceptMode::kBalanced;
     std::vector<int> cpu_affinity;    // optional: worker i is pinned to cpu_affinity[i % size]
     int shutdown_grace_ms = 5000;     // in-flight work gets this long to finish after SIGTERM
     int drain_linger_ms = 100;        // idle keep-alive connections stay answerable this long (see begin_drain)
@@ -128,6 +143,15 @@ struct WorkerStats {
     std::atomic<uint64_t> connections_open{0};
     std::atomic<uint64_t> requests{0};
     std::atomic<uint64_t> bad_requests{0};
+};
+
+// Snapshot of one worker (Server::worker_stats): what shows whether the load is spread evenly.
+struct WorkerSnapshot {
+    int id = 0;
+    uint64_t connections_accepted = 0;  // connections this worker has served (adopted), not accept() calls
+    uint64_t connections_open = 0;
+    uint64_t requests = 0;
+    double cpu_seconds = 0;             // CPU time of the worker's thread so far
 };
 
 struct ServerStats {
@@ -173,7 +197,8 @@ class Worker final : public EventHandler {
     friend class Server;
     friend class Connection;
     bool open_listener(std::string* error);
-    void adopt(int fd);  // loop thread
+    void adopt(int fd);  // loop thread; the caller has already counted the connection in connections_open
+    Worker* least_loaded();
     void release(Connection* c);
     void begin_drain();
     void thread_main();
@@ -190,11 +215,12 @@ class Worker final : public EventHandler {
     std::vector<uint32_t> free_;
     std::vector<uint32_t> parked_;  // closed in this loop iteration; joins free_ when the iteration ends
     size_t open_count_ = 0;
-    std::vector<Worker*>* peers_ = nullptr;  // round-robin mode: all workers
+    std::vector<Worker*>* peers_ = nullptr;  // all workers, when this one may hand connections to others
     size_t rr_next_ = 0;
     int64_t date_second_ = -1;
     char date_[29];
     void* app_state_ = nullptr;
+    std::atomic<double> cpu_seconds_{0};  // filled in when the thread exits
     std::thread thread_;
 };
 
@@ -211,6 +237,7 @@ class Server {
     uint16_t port() const { return bound_port_; }
     int threads() const { return static_cast<int>(workers_.size()); }
     ServerStats stats() const;
+    std::vector<WorkerSnapshot> worker_stats() const;
     Worker& worker(int i) { return *workers_[static_cast<size_t>(i)]; }
 
  private:

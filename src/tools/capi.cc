@@ -412,6 +412,11 @@ void hola_service_trace_stats(const hola_service* s, uint64_t* reported, uint64_
     if (dropped) *dropped = st.spans_dropped;
 }
 
+int hola_service_stats_json(const hola_service* s, char** out, size_t* out_len) {
+    give(s->service->stats_json(), out, out_len);
+    return 0;
+}
+
 void hola_service_stop(hola_service* s) {
     if (!s) return;
     s->service->stop();

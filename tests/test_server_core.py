@@ -143,13 +143,47 @@ def test_many_concurrent_connections(hola_server):
     assert not errors
 
 
-@pytest.mark.parametrize("mode", ["reuseport", "rr"])
+@pytest.mark.parametrize("mode", ["balanced", "reuseport", "rr"])
 def test_accept_modes(hola_server, mode):
     srv = hola_server(args=["--accept-mode", mode], threads=3)
     conns = [client.Connection("127.0.0.1", srv.port) for _ in range(9)]
     try:
         for c in conns:
             assert c.request("GET", "/api/hola").body == HOLA
+        stats = srv.stats()
+        assert stats["accept_mode"] == mode and stats["connections_open"] == 9 and stats["requests"] == 9
+        per_worker = [w["connections_open"] for w in stats["workers"]]
+        assert sum(per_worker) == 9
+        if mode != "reuseport":  # the kernel's hash makes no promise; the other two modes do
+            assert per_worker == [3, 3, 3]
+    finally:
+        for c in conns:
+            c.close()
+
+
+def test_default_placement_spreads_keep_alive_connections_evenly(hola_server):
+    """64 keep-alive clients over 16 workers is the benchmark's shape (BASELINE.json config 4 on a
+    32-vCPU box). Undertow deals connections to its I/O threads in turn; hashing them over
+    SO_REUSEPORT listeners leaves some workers with one connection and others with eight."""
+    srv = hola_server(threads=16)
+    conns = [client.Connection("127.0.0.1", srv.port) for _ in range(64)]
+    try:
+        for c in conns:
+            assert c.request("GET", "/api/hola").body == HOLA
+        stats = srv.stats()
+        assert stats["accept_mode"] == "balanced"
+        assert [w["connections_open"] for w in stats["workers"]] == [4] * 16
+        assert [w["requests"] for w in stats["workers"]] == [4] * 16
+        # Closing some and opening others keeps the spread within one connection.
+        for c in conns[:20]:
+            c.close()
+        del conns[:20]
+        time.sleep(0.2)
+        conns += [client.Connection("127.0.0.1", srv.port) for _ in range(20)]
+        for c in conns[-20:]:
+            assert c.request("GET", "/api/health").body == b"I'm ok"
+        per_worker = [w["connections_open"] for w in srv.stats()["workers"]]
+        assert sum(per_worker) == 64 and max(per_worker) - min(per_worker) <= 1, per_worker
     finally:
         for c in conns:
             c.close()

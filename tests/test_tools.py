@@ -97,14 +97,49 @@ def test_bench_prints_one_contract_line():
     assert r["config"]["connections_per_instance"] == 64
     assert r["latency_us"]["p50"] <= r["latency_us"]["p99"]
     assert "GET /api/hola" in r["metric"]
+    # The keys that make the line readable on its own.
+    assert r["server_cores_total"] == len(r["config"]["server_cpus"]) >= 1
+    assert abs(r["per_server_core_rps"] * r["server_cores_total"] - r["value"]) < r["server_cores_total"]
+    assert r["config"]["accept_mode"] == "balanced" and 1.0 <= r["worker_spread"] < 2.0
+    assert sum(r["config"]["worker_connections"]) == 64
+    assert max(r["config"]["worker_connections"]) - min(r["config"]["worker_connections"]) <= 1
+    assert r["spans"]["dropped"] > 0 and r["spans"]["reported"] == 0  # as-is: every span goes to a collector nobody runs
+    assert 0.05 < r["coldstart_ms"]["median"] < 2000 and r["coldstart_ms"]["runs"] == 5
+    assert "cold_start_s" not in r["config"] and "listen_log_s" in r["config"]
+    hk = r["config"]["housekeeping_cpu"]
+    if len(os.sched_getaffinity(0)) >= 4:
+        assert hk is not None and hk not in r["config"]["server_cpus"] and hk not in r["config"]["load_cpus"]
 
 
 def test_bench_reference_arm_reports_unavailable():
+    env = {k: v for k, v in os.environ.items() if k != "HOLA_REFERENCE_CMD"}
     out = subprocess.run([sys.executable, str(REPO / "bench.py"), "--impl", "reference", "--gpus", "1", "--steps", "1", "--warmup", "1"],
-                         capture_output=True, text=True, timeout=60)
+                         capture_output=True, text=True, timeout=60, env=env)
     assert out.returncode == 0
     r = json.loads(out.stdout.strip().splitlines()[-1])
     assert r["impl"] == "reference" and "unavailable" in r and len(r["unavailable"]) > 20
+
+
+@pytest.mark.slow
+def test_bench_reference_arm_drives_another_program_through_the_same_procedure():
+    """No box has a JVM, so the reference arm has never met the real jar. What can be shown is
+    that the arm is wired: given a launch command (HOLA_REFERENCE_CMD, or java + the jar under
+    baseline/_ref) it starts that program pinned to the server CPUs, waits for its first 200, runs
+    the identical hola-load invocation and prints the same schema - here against a stand-in that
+    is not this repository's server. Two such lines are all the driver needs for a ratio."""
+    standin = "%s %s {port}" % (sys.executable, REPO / "tests" / "data" / "standin_reference.py")
+    ref = _run_bench("--impl", "reference", "--steps", "2", "--warmup", "3", "--coldstart-runs", "2", "--half-load-seconds", "0",
+                     env={"HOLA_REFERENCE_CMD": standin})
+    ours = _run_bench("--steps", "2", "--warmup", "3", "--coldstart-runs", "2", "--half-load-seconds", "0")
+    assert ref["impl"] == "reference" and ours["impl"] == "ours"
+    assert set(ref) == set(ours) and set(ref["config"]) == set(ours["config"])
+    for key in ("metric", "unit", "n_gpus", "steps", "warmup", "data"):
+        assert ref[key] == ours[key]
+    assert ref["config"]["server_cpus"] == ours["config"]["server_cpus"] and ref["config"]["load_cpus"] == ours["config"]["load_cpus"]
+    assert ref["value"] > 100 and ref["requests"] > 200 and ref["errors"] == 0
+    assert ref["coldstart_ms"]["median"] > ours["coldstart_ms"]["median"]  # an interpreter starts slower than the executable
+    assert ref["worker_spread"] is None and ref["spans"] is None          # nothing the reference can be asked for
+    assert ours["value"] / ref["value"] > 1.0                             # the ratio exists (and a Python stand-in is slow)
 
 
 @pytest.mark.slow
