@@ -379,9 +379,11 @@ void HolaApp::serve_static_file(WorkerState& st, Connection& conn, const Request
     constexpr size_t kStaticCacheBytes = 64u << 20;
     Worker& worker = *st.worker;
     const bool head_only = rq.method == Method::kHead;
-    std::string rel;
-    bool ok = percent_decode(rq.path.substr(8), &rel);  // keeps the leading '/'
-    if (ok) {
+    // rq.path is canonical already: decoded (but for %2F/%5C, which then simply name no file),
+    // matrix parameters cut, dot segments resolved.
+    const std::string rel(rq.path.substr(8));  // keeps the leading '/'
+    bool ok = true;
+    {
         // No hidden files, no NULs, no backslashes (the resolved-path check below does the rest).
         if (rel.find('\0') != std::string::npos || rel.find("/.") != std::string::npos || rel.find('\\') != std::string::npos)
             ok = false;

@@ -167,6 +167,25 @@ ParseStatus parse_request_head(const char* data, size_t len, RequestHead* out) {
         out->path = target.substr(0, q);
         out->query = target.substr(q + 1);
     }
+    out->raw_path = out->path;
+    // One pass over a path that is a dozen bytes long: anything that canonicalise_path() would
+    // change? (The common request - /api/hola - has nothing of the kind and keeps its view.)
+    {
+        const std::string_view p = out->path;
+        for (size_t i = 0; i < p.size(); ++i) {
+            const char c = p[i];
+            if (c == '%' || c == ';') {
+                out->path_is_canonical = false;
+                break;
+            }
+            if (c == '/' && i + 1 < p.size() && (p[i + 1] == '/' || p[i + 1] == '.')) {
+                // "//", or a segment that starts with a dot: "/.", "/..", but also "/.well-known" -
+                // the slow path sorts those out.
+                out->path_is_canonical = false;
+                break;
+            }
+        }
+    }
 
     // Headers.
     bool saw_content_length = false;
@@ -497,6 +516,55 @@ bool percent_decode(std::string_view in, std::string* out) {
         out->push_back(static_cast<char>((hex_value(in[i + 1]) << 4) | hex_value(in[i + 2])));
         i += 2;
     }
+    return true;
+}
+
+bool canonicalise_path(std::string_view raw, std::string* out) {
+    out->clear();
+    if (raw.empty() || raw[0] != '/') {  // "*" (OPTIONS *) and the like: nothing to canonicalise
+        out->assign(raw);
+        return true;
+    }
+    out->reserve(raw.size());
+    std::string segment;
+    size_t i = 1;
+    bool trailing_slash = raw.size() > 1 && raw.back() == '/';
+    while (i <= raw.size()) {
+        size_t end = raw.find('/', i);
+        if (end == std::string_view::npos) end = raw.size();
+        std::string_view seg = raw.substr(i, end - i);
+        const size_t semi = seg.find(';');
+        if (semi != std::string_view::npos) seg = seg.substr(0, semi);
+        segment.clear();
+        for (size_t k = 0; k < seg.size(); ++k) {
+            if (seg[k] != '%') {
+                segment.push_back(seg[k]);
+                continue;
+            }
+            if (k + 2 >= seg.size()) return false;
+            if (!is_hex_digit(seg[k + 1]) || !is_hex_digit(seg[k + 2])) return false;
+            const int v = (hex_value(seg[k + 1]) << 4) | hex_value(seg[k + 2]);
+            if (v == 0) return false;
+            if (v == '/' || v == '\\') {
+                segment.append(seg.substr(k, 3));  // stays encoded
+            } else {
+                segment.push_back(static_cast<char>(v));
+            }
+            k += 2;
+        }
+        if (segment.empty() || segment == ".") {
+            if (end == raw.size() && !segment.empty()) trailing_slash = true;  // "/a/." names the directory "/a/"
+        } else if (segment == "..") {
+            const size_t cut = out->rfind('/');
+            if (cut != std::string::npos) out->resize(cut);
+            if (end == raw.size()) trailing_slash = true;
+        } else {
+            out->push_back('/');
+            out->append(segment);
+        }
+        i = end + 1;
+    }
+    if (out->empty() || (trailing_slash && out->back() != '/')) out->push_back('/');
     return true;
 }
 

@@ -24,7 +24,10 @@ struct RequestHead {
     Method method = Method::kOther;
     std::string_view method_text;
     std::string_view target;  // as sent
-    std::string_view path;    // target up to '?', scheme://authority stripped for absolute-form
+    std::string_view path;    // target up to '?', scheme://authority stripped for absolute-form; the server core
+                              // replaces it with the canonical form (canonicalise_path) before routing
+    std::string_view raw_path;  // always as sent
+    bool path_is_canonical = true;  // false: contains '%', ';', '//' or a dot segment - canonicalise before routing
     std::string_view query;   // after '?', may be empty
     int version_minor = 1;
     bool keep_alive = true;
@@ -85,5 +88,20 @@ void format_http_date(int64_t unix_seconds, char out[29]);
 
 // Percent-decodes a path. Returns false on malformed escapes.
 bool percent_decode(std::string_view in, std::string* out);
+
+// The path a request is routed by, from the path as sent. The reference's container does this
+// before any resource is matched: Undertow percent-decodes the request path and resolves "." and
+// ".." segments and empty segments, and path (matrix) parameters - ";name=value" at the end of a
+// segment - are not part of the path RESTEasy matches (@ApplicationPath/@Path,
+// /root/reference/src/main/java/com/redhat/developers/msa/hola/JaxRsActivator.java:30,
+// HolaResource.java:46,52-53,69-70,80-81). So /api/%68ola, /api/hola;v=1 and /api/../api/hola are
+// all GET /api/hola.
+//   1. per segment: cut at the first ';'
+//   2. percent-decode, except %2F and %5C (an encoded slash stays encoded, as with Undertow's
+//      default allow-encoded-slash=false, so it can never introduce a segment boundary)
+//   3. drop "." and empty segments, let ".." remove the segment before it (never above the root)
+// A trailing slash is kept. Returns false - the request is answered 400 - for a malformed escape
+// or a decoded NUL byte.
+bool canonicalise_path(std::string_view raw, std::string* out);
 
 }  // namespace hola

@@ -218,6 +218,18 @@ void Connection::process_input() {
             break;
         }
         in_pos_ += head.head_len;
+        if (!head.path_is_canonical) {
+            // Route by the path the reference's container would route by (core/http.h,
+            // canonicalise_path); the path as sent stays available as raw_path and target.
+            if (!canonicalise_path(head.raw_path, &worker_->canonical_path_)) {
+                bump(worker_->stats_.bad_requests);
+                append_core_error(&out_, 400, "Bad Request", worker_->http_date());
+                close_after_write_ = true;
+                break;
+            }
+            head.path = worker_->canonical_path_;
+            head.path_is_canonical = true;
+        }
         if (head.chunked) {
             discard_chunked_.reset(new ChunkedDecoder());
         } else if (head.content_length > 0) {

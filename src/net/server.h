@@ -219,6 +219,7 @@ class Worker final : public EventHandler {
     size_t rr_next_ = 0;
     int64_t date_second_ = -1;
     char date_[29];
+    std::string canonical_path_;  // scratch for the request being dispatched
     void* app_state_ = nullptr;
     std::atomic<double> cpu_seconds_{0};  // filled in when the thread exits
     std::thread thread_;

@@ -314,6 +314,13 @@ int hola_http_parse_request(const char* data, size_t len, char** out, size_t* ou
     json_kn(&o, "method_id", static_cast<int>(h.method));
     json_kv(&o, "target", h.target);
     json_kv(&o, "path", h.path);
+    std::string canonical;
+    if (canonicalise_path(h.raw_path, &canonical)) {
+        json_kv(&o, "canonical_path", canonical);
+    } else {
+        o.append(",\"canonical_path\":null");
+    }
+    json_kb(&o, "path_is_canonical", h.path_is_canonical);
     json_kv(&o, "query", h.query);
     json_kn(&o, "version_minor", h.version_minor);
     json_kb(&o, "keep_alive", h.keep_alive);

@@ -512,6 +512,60 @@ TEST(http_percent_decode) {
     CHECK_EQ(out, std::string("/endA"));
 }
 
+TEST(http_canonical_path) {
+    struct Case { const char* raw; const char* want; } cases[] = {
+        {"/api/hola", "/api/hola"},
+        {"/api/%68ola", "/api/hola"},                      // percent-decoded
+        {"/api/hola;a=1", "/api/hola"},                    // matrix parameters are not part of the path
+        {"/api;x=1;y/hola;v=2/", "/api/hola/"},            // ... in any segment; trailing slash kept
+        {"/api/../api/health", "/api/health"},             // dot segments
+        {"/api/./hola", "/api/hola"},
+        {"/api//hola", "/api/hola"},                       // empty segments
+        {"/../../api/hola", "/api/hola"},                  // never above the root
+        {"/api/%2e%2e/api/%2E/hola", "/api/hola"},         // decoded first, then resolved
+        {"/webjars/..%2f..%2fsecret.txt", "/webjars/..%2f..%2fsecret.txt"},  // an encoded slash is no segment boundary
+        {"/a%5Cb", "/a%5Cb"},
+        {"/api/hola%3Bx", "/api/hola;x"},                  // an encoded semicolon is data
+        {"/api/hola/.", "/api/hola/"},
+        {"/api/hola/..", "/api/"},
+        {"/", "/"},
+        {"/..", "/"},
+        {"/.well-known/x", "/.well-known/x"},
+        {"/a%20b/%7Ec", "/a b/~c"},
+        {"*", "*"},
+    };
+    std::string out;
+    for (const auto& c : cases) {
+        CHECK(canonicalise_path(c.raw, &out));
+        CHECK_EQ(out, std::string(c.want));
+        // Canonical form is a fixed point (an encoded slash stays encoded, so it is stable too) -
+        // except where decoding produced a literal ';', which a second pass would take for a parameter.
+        std::string again;
+        CHECK(canonicalise_path(out, &again));
+        if (out.find(';') == std::string::npos) CHECK_EQ(again, out);
+    }
+    CHECK(!canonicalise_path("/bad%2", &out));
+    CHECK(!canonicalise_path("/bad%zz", &out));
+    CHECK(!canonicalise_path("/bad%", &out));
+    CHECK(!canonicalise_path("/nul%00byte", &out));
+    // The parser flags exactly the paths that need the slow path.
+    auto flagged = [](const char* target) {
+        const std::string rq = std::string("GET ") + target + " HTTP/1.1\r\n\r\n";
+        RequestHead h;
+        CHECK(parse_request_head(rq.data(), rq.size(), &h) == ParseStatus::kComplete);
+        CHECK_EQ(std::string(h.raw_path), std::string(h.path));
+        return !h.path_is_canonical;
+    };
+    CHECK(!flagged("/api/hola"));
+    CHECK(!flagged("/api/hola?x=%41;y=/../"));  // the query is not the path
+    CHECK(!flagged("/webjars/swagger-ui/2.1.4/swagger-ui.js"));
+    CHECK(flagged("/api/%68ola"));
+    CHECK(flagged("/api/hola;a=1"));
+    CHECK(flagged("/api/../api/health"));
+    CHECK(flagged("/api//hola"));
+    CHECK(flagged("/api/hola/."));
+}
+
 // ---- trace -------------------------------------------------------------------------------------
 
 TEST(trace_ids_and_decisions) {

@@ -15,6 +15,9 @@ CONF = os.path.join(DATA, "translation.properties")
 REFERENCE_CONF = "/root/reference/translation.properties"
 
 
+HOLA = b"Hola de unknown"
+
+
 def get(srv, target, **kw):
     return client.get("127.0.0.1", srv.port, target, **kw)
 
@@ -218,6 +221,38 @@ def test_swagger_document(hola_server):
     assert b'"swagger" : "2.0"' in r.body  # setPrettyPrint(true)
     y = get(srv, "/api/swagger.yaml")
     assert y.status == 200 and b'swagger: "2.0"' in y.body and b"/hola-chaining:" in y.body
+
+
+def test_request_path_is_canonicalised_before_routing(hola_server, fake_zipkin):
+    """Undertow decodes and normalises the request path, and RESTEasy matches it without matrix
+    parameters (JaxRsActivator.java:30, HolaResource.java:46,52-53,69-70,80-81): these spellings
+    all name the same three resources. The path as sent survives where the reference would show
+    it: in RESTEasy's 404 text and in the span's http.url tag."""
+    srv = hola_server(env={"ZIPKIN_SERVER_URL": fake_zipkin.url}, args=["--zipkin-flush-ms", "50"])
+    for target in ("/api/%68ola", "/api/hola;a=1", "/api/../api/hola", "/api//hola", "/api/./hola", "/api;v=2/hola", "/%61pi/hol%61",
+                   "/api/x/../hola", "//api/hola", "/api/%2e%2e/api/hola"):
+        r = get(srv, target)
+        assert (r.status, r.body) == (200, HOLA), target
+        assert r.header("Access-Control-Allow-Origin") == "*"
+    assert get(srv, "/api/../api/health").body == b"I'm ok"
+    assert get(srv, "/api/%68ealth;probe=1?x=1").body == b"I'm ok"
+    assert get(srv, "/api/hola-chaining/../swagger.json").header("Content-Type") == "application/json"
+    assert get(srv, "/./index.html").status == 200 and get(srv, "/x/..").status == 200  # the landing page
+    # Not the same resource: an encoded slash is no separator, an encoded semicolon no parameter.
+    assert get(srv, "/api%2Fhola").status == 404
+    assert get(srv, "/api/hola%3Ba=1").status == 404
+    assert get(srv, "/api/hola/extra/..;x").status == 200  # "..;x" is ".." once its parameters are cut
+    # Malformed escapes and NUL bytes are refused outright.
+    for target in ("/api/hola%", "/api/hola%4", "/api/hola%zz", "/api/hola%00"):
+        r = get(srv, target)
+        assert r.status == 400 and r.header("Connection") == "close", target
+    # The 404 text quotes the URL as it was sent.
+    r = get(srv, "/api/no%74here;p=1")
+    assert r.status == 404 and b"/api/no%74here;p=1" in r.body
+    # Tracing stays mapped on the canonical URL (ZipKinFilter.java:43) and reports the URL as sent.
+    urls = sorted(s["binaryAnnotations"][0]["value"] for s in fake_zipkin.wait_for_spans(12))
+    assert "http://localhost/api/%68ola" in urls and "http://localhost/api/hola;a=1" in urls
+    assert not any("health" in u or "swagger" in u for u in urls)
 
 
 def test_webjars_directory(hola_server, tmp_path):

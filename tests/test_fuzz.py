@@ -103,6 +103,9 @@ def test_random_valid_pipelines_match_a_model(hola_server, fake_aloha):
         (client.build_request("GET", "/api/hola"), (200, b"Hola de unknown")),
         (client.build_request("GET", "/api/hola?x=%d" % 7), (200, b"Hola de unknown")),
         (client.build_request("GET", "/api/health"), (200, b"I'm ok")),
+        (client.build_request("GET", "/api/%68ola;v=1"), (200, b"Hola de unknown")),   # canonicalised before routing
+        (client.build_request("GET", "/api/../api/./health"), (200, b"I'm ok")),
+        (client.build_request("GET", "/api/hola%zz"), None),                           # 400, and the connection is closed
         (client.build_request("HEAD", "/api/hola"), (200, b"")),
         (client.build_request("GET", "/api/hola-chaining"), (200, chained)),
         (client.build_request("POST", "/api/hola", body=b"GET /api/health HTTP/1.1\r\n\r\n"), (405, b"")),
@@ -115,6 +118,10 @@ def test_random_valid_pipelines_match_a_model(hola_server, fake_aloha):
     rng = random.Random(4242)
     for round_no in range(25):
         picks = [rng.choice(menu) for _ in range(rng.randint(1, 30))]
+        # A malformed path ends the connection: everything before it is answered, then a 400.
+        fatal = next((i for i, p in enumerate(picks) if p[1] is None), None)
+        if fatal is not None:
+            picks = picks[:fatal + 1]
         wire = b"".join(p[0] for p in picks)
         with client.Connection("127.0.0.1", srv.port, timeout=10) as c:
             pos = 0
@@ -122,13 +129,19 @@ def test_random_valid_pipelines_match_a_model(hola_server, fake_aloha):
                 step = rng.choice([1, 2, 3, 7, 20, 100, 1000, len(wire)])
                 c.send_raw(wire[pos:pos + step])
                 pos += step
-            for i, (raw, (status, body)) in enumerate(picks):
+            for i, (raw, expected) in enumerate(picks):
+                if expected is None:
+                    r = c.read_response()
+                    assert r.status == 400 and c.closed_by_peer(), (round_no, i)
+                    break
+                status, body = expected
                 r = c.read_response(head_only=raw.startswith(b"HEAD"))
                 assert r.status == status, (round_no, i, raw[:40], r.status)
                 if body is not None:
                     assert r.body == body, (round_no, i, raw[:40], r.body)
             # Nothing extra was produced, and the connection is still in sync.
-            assert c.request("GET", "/api/health").body == b"I'm ok"
+            if fatal is None:
+                assert c.request("GET", "/api/health").body == b"I'm ok"
 
 
 def test_random_bytes_and_huge_lines(hola_server):

@@ -440,6 +440,57 @@ def test_http_request_parser_roundtrip(method, path, query, headers, trailing):
         assert native.http_parse_request(raw[:cut])[0] == "incomplete"
 
 
+def _model_canonical(raw: str):
+    """Independent restatement of core/http.h canonicalise_path: cut matrix parameters, decode
+    (not %2F/%5C), resolve dot and empty segments; None for a malformed escape or a decoded NUL."""
+    import re
+    trailing = len(raw) > 1 and raw.endswith("/")
+    stack = []
+    segs = raw[1:].split("/")
+    for idx, seg in enumerate(segs):
+        seg = seg.split(";", 1)[0]
+        if re.search(r"%(?![0-9a-fA-F]{2})", seg):
+            return None
+        if re.search(r"%00", seg):
+            return None
+        seg = re.sub(r"%([0-9a-fA-F]{2})", lambda m: m.group(0) if m.group(1).lower() in ("2f", "5c") else chr(int(m.group(1), 16)), seg)
+        last = idx == len(segs) - 1
+        if seg == "" or seg == ".":
+            if last and seg == ".":
+                trailing = True
+        elif seg == "..":
+            if stack:
+                stack.pop()
+            if last:
+                trailing = True
+        else:
+            stack.append(seg)
+    out = "".join("/" + x for x in stack)
+    if out == "" or (trailing and not out.endswith("/")):
+        out += "/"
+    return out
+
+
+_PATH_PIECES = st.sampled_from(["api", "hola", "health", ".", "..", "", "%68ola", "hol%61", "%2e", "%2E%2e", ";a=1", "hola;v=2;w",
+                                "..;x", "%2f", "%5C", "%3B", "a%20b", "~", "%7e", "%", "%4", "%zz", "%00", "x%41%42", "-_.!"])
+
+
+@settings(max_examples=400, deadline=None)
+@given(st.lists(_PATH_PIECES, min_size=0, max_size=7), st.booleans())
+def test_canonical_path_matches_the_model(pieces, trailing_slash):
+    raw = "/" + "/".join(pieces) + ("/" if trailing_slash else "")
+    state, info = native.http_parse_request(("GET %s HTTP/1.1\r\n\r\n" % raw).encode("latin-1"))
+    assert state == "complete" and info["path"] == raw
+    want = _model_canonical(raw)
+    got = info["canonical_path"]
+    assert (got.encode("latin-1").decode("latin-1") if got is not None else None) == want, raw
+    if want is not None:
+        assert want.startswith("/") and "//" not in want
+        assert not any(seg in (".", "..") for seg in want.split("/"))
+    if info["path_is_canonical"]:
+        assert want == raw  # the fast path is only taken when there is nothing to do
+
+
 @settings(max_examples=200, deadline=None)
 @given(st.lists(st.binary(min_size=1, max_size=50), max_size=6), st.binary(max_size=10))
 def test_dechunk_roundtrip(chunks, rest):
