@@ -118,6 +118,9 @@ HolaApp::HolaApp(AppOptions options, GreetingService* greeting, Tracer* tracer, 
                options_.breaker) {
     const std::string authority = authority_of(options_);
     aloha_stand_in_body_ = json_encode_string_list({std::string("Aloha mai ") + options_.hostname});
+    fallback_json_tail_ = ",";
+    json_append_string(&fallback_json_tail_, options_.fallback);
+    fallback_json_tail_.push_back(']');
     aloha_url_ = "http://" + authority + options_.aloha_path;
     if (!options_.webjars_dir.empty()) {
         char resolved[PATH_MAX];

@@ -46,6 +46,9 @@ struct AppOptions {
     int stream_max_connections = 5;               // hystrix.stream.maxConcurrentConnections default
     int stream_default_delay_ms = 500;
     bool verbose = false;
+    // Feign's Logger.Level.BASIC lines on stderr for every downstream call, as the reference
+    // configures them (HolaResource.java:109). Off by default: see DESIGN.md section 5.
+    bool log_feign = false;
     bool serve_aloha = false;  // also answer GET /api/aloha-chaining like the next service of the demo would
 };
 
@@ -66,6 +69,7 @@ class HolaApp final : public Application {
  private:
     struct WorkerState;
     struct ChainCall;
+    class CallRef;
     struct StreamSub;
 
     static WorkerState& state_of(Worker& w) { return *static_cast<WorkerState*>(w.app_state()); }
@@ -80,10 +84,14 @@ class HolaApp final : public Application {
     const GreetingSnapshot& current_greeting(WorkerState& st);
 
     // Downstream call with breaker, timeout and fallback.
-    void start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call);
-    void send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCall>& call);
-    void finish_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call, JsonStringList&& tail);
-    JsonStringList fallback_tail(ChainCall& call) const;
+    CallRef new_call(WorkerState& st);
+    void start_chain(WorkerState& st, const CallRef& call);
+    void send_chain_attempt(WorkerState& st, const CallRef& call);
+    // `tail` null: the call failed, timed out or was refused - the fallback (or, with fallbacks
+    // switched off, a 500) is the answer.
+    void finish_chain(WorkerState& st, const CallRef& call, const JsonStringList* tail);
+    void append_chain_body(std::string* out, std::string_view hola_text, const JsonStringList* tail) const;
+    void append_fallback_response(WorkerState& st, Connection& conn, const RequestHead& rq, const GreetingSnapshot& g);
 
     // Tracing.
     void record_span(WorkerState& st, const TraceContext& ctx, bool client, int64_t start_us, int64_t end_us,
@@ -103,6 +111,7 @@ class HolaApp final : public Application {
     std::string aloha_request_prefix_;  // request line + fixed headers, B3 headers are appended
     std::string aloha_url_;             // for the client span's http.url tag
     std::string aloha_stand_in_body_;   // what --serve-aloha answers on /api/aloha-chaining
+    std::string fallback_json_tail_;    // `,"<fallback>"]` - the end of the body when the downstream call did not succeed
 
     // /webjars/**: resolved root and an in-memory copy of the files served so far.
     struct StaticFile {

@@ -6,6 +6,8 @@
 #include <string>
 #include <string_view>
 #include <unordered_map>
+#include <utility>
+#include <vector>
 
 #include "app/hola_app.h"
 
@@ -40,7 +42,29 @@ struct HolaApp::StreamSub {
     EventLoop::TimerId timer = 0;
 };
 
+// Reference to a pooled ChainCall (intrusive count; single-threaded: a call lives on one event
+// loop). The last reference hands the object back to its worker's pool, where it keeps the
+// capacity of its strings for the next call.
+class HolaApp::CallRef {
+ public:
+    CallRef() = default;
+    explicit CallRef(ChainCall* p);
+    CallRef(const CallRef& o);
+    CallRef(CallRef&& o) noexcept : p_(o.p_) { o.p_ = nullptr; }
+    CallRef& operator=(CallRef o) noexcept {
+        std::swap(p_, o.p_);
+        return *this;
+    }
+    ~CallRef();
+    ChainCall* operator->() const { return p_; }
+    ChainCall& operator*() const { return *p_; }
+
+ private:
+    ChainCall* p_ = nullptr;
+};
+
 struct HolaApp::WorkerState {
+    ~WorkerState();
     Worker* worker = nullptr;
     IdGenerator ids;
     SpanRing* ring = nullptr;
@@ -65,9 +89,20 @@ struct HolaApp::WorkerState {
     bool accept_yaml = true;
 
     std::unordered_map<uint64_t, StreamSub> streams;
+
+    // GET /api/hola-chaining.
+    std::vector<ChainCall*> call_pool;   // idle ChainCall objects (owned)
+    std::string fallback_bytes;          // ready-to-send keep-alive response of the fallback outcome
+    size_t fallback_date_at = 0;
+    int64_t fallback_second = -1;
+    uint64_t fallback_version = 0;
+    std::string scratch;                 // response under construction
 };
 
 struct HolaApp::ChainCall {
+    int refs = 0;
+    WorkerState* owner = nullptr;
+    std::shared_ptr<const GreetingSnapshot> greeting;  // element 0 of the answer is its text
     ConnRef ref;
     bool head_only = false;
     bool close = false;
@@ -75,7 +110,6 @@ struct HolaApp::ChainCall {
     bool settled = false;   // the downstream outcome has been decided
     bool finished = false;  // the response has been produced
     std::string response;   // filled when finishing before handle() returns
-    std::string hola_text;
     TraceContext server_ctx;
     TraceContext client_ctx;
     std::string server_url;
@@ -87,6 +121,37 @@ struct HolaApp::ChainCall {
     EventLoop::TimerId retry_timer = 0;  // pause before the next attempt
     int attempt = 0;
     bool failed_without_fallback = false;
+
+    // Back to the state of a fresh object, keeping the strings' storage.
+    void recycle() {
+        greeting.reset();
+        ref = ConnRef{};
+        head_only = close = deferred = settled = finished = failed_without_fallback = false;
+        response.clear();
+        server_ctx = TraceContext{};
+        client_ctx = TraceContext{};
+        server_url.clear();
+        server_start_us = client_start_us = exec_start_ns = 0;
+        request = 0;
+        timer = retry_timer = 0;
+        attempt = 0;
+    }
 };
+
+inline HolaApp::CallRef::CallRef(ChainCall* p) : p_(p) {
+    if (p_) ++p_->refs;
+}
+inline HolaApp::CallRef::CallRef(const CallRef& o) : p_(o.p_) {
+    if (p_) ++p_->refs;
+}
+inline HolaApp::CallRef::~CallRef() {
+    if (p_ && --p_->refs == 0) {
+        p_->recycle();
+        p_->owner->call_pool.push_back(p_);
+    }
+}
+inline HolaApp::WorkerState::~WorkerState() {
+    for (ChainCall* c : call_pool) delete c;
+}
 
 }  // namespace hola

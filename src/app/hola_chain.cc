@@ -1,7 +1,18 @@
 // GET /api/hola-chaining: the downstream call with circuit breaker, bulkhead, timeout, Feign-style
 // retries and static fallback (/root/reference/src/main/java/com/redhat/developers/msa/hola/HolaResource.java:69-78, 94-113;
 // /root/reference/src/main/resources/config.properties:17,19).
+//
+// Cost model. The reference builds a new HTTP client, a new Feign proxy and a new Hystrix command
+// per request (HolaResource.java:94-113). Here the three outcomes cost:
+//   * refused by the breaker or the bulkhead (what a dead `aloha` turns every request into once
+//     the circuit is open): no allocation, no shared lock - the breaker's counters are sharded per
+//     event loop (core/breaker.h) and the fallback answer is a pre-rendered byte string per worker
+//     and greeting version, exactly like the /api/hola answer;
+//   * the downstream call runs: one pooled ChainCall object per request (recycled with the
+//     capacity of its strings), one pooled keep-alive connection, one timer;
+//   * fallbacks switched off and the call fails: a 500, rendered on the spot.
 #include <cstdio>
+#include <cstring>
 
 #include "app/hola_app_internal.h"
 
@@ -22,29 +33,110 @@ void append_b3_id(std::string* out, const char* name, uint64_t id) {
 
 }  // namespace
 
+HolaApp::CallRef HolaApp::new_call(WorkerState& st) {
+    ChainCall* c;
+    if (!st.call_pool.empty()) {
+        c = st.call_pool.back();
+        st.call_pool.pop_back();
+    } else {
+        c = new ChainCall();
+        c->owner = &st;
+    }
+    return CallRef(c);
+}
+
+// ["<hola text>", ...tail] or, without a tail, ["<hola text>","<fallback>"] - compact, as
+// json_encode_string_list writes it, without building the list first.
+void HolaApp::append_chain_body(std::string* out, std::string_view hola_text, const JsonStringList* tail) const {
+    out->push_back('[');
+    json_append_string(out, hola_text);
+    if (!tail) {
+        out->append(fallback_json_tail_);
+        return;
+    }
+    for (const auto& item : *tail) {
+        out->push_back(',');
+        if (item) {
+            json_append_string(out, *item);
+        } else {
+            out->append("null");
+        }
+    }
+    out->push_back(']');
+}
+
+// The answer of every request that did not get a downstream reply, when fallbacks are on: the
+// static fallback list (HolaResource.java:112) after the greeting.
+void HolaApp::append_fallback_response(WorkerState& st, Connection& conn, const RequestHead& rq, const GreetingSnapshot& g) {
+    Worker& worker = *st.worker;
+    if (rq.method == Method::kGet && !conn.closing()) {
+        const int64_t second = worker.loop().now_unix_s();
+        if (st.fallback_version != g.version || st.fallback_bytes.empty()) {
+            st.scratch.clear();
+            append_chain_body(&st.scratch, g.text, nullptr);
+            st.fallback_bytes.clear();
+            st.fallback_date_at = append_response(&st.fallback_bytes, 200, kJson, st.scratch, true, false, false, worker.http_date());
+            st.fallback_version = g.version;
+            st.fallback_second = second;
+        } else if (second != st.fallback_second) {
+            std::memcpy(&st.fallback_bytes[st.fallback_date_at], worker.http_date().data(), 29);
+            st.fallback_second = second;
+        }
+        conn.out().append(st.fallback_bytes);
+        return;
+    }
+    st.scratch.clear();
+    append_chain_body(&st.scratch, g.text, nullptr);
+    append_response(&conn.out(), 200, kJson, st.scratch, true, conn.closing(), rq.method == Method::kHead, worker.http_date());
+}
+
 Disposition HolaApp::serve_chaining(WorkerState& st, Connection& conn, const RequestHead& rq) {
     Worker& worker = *st.worker;
     const GreetingSnapshot& g = current_greeting(st);
     const bool traced = st.ring != nullptr && rq.path.size() == 18;  // exactly "/api/hola-chaining"
-    auto call = std::make_shared<ChainCall>();
-    call->ref = conn.ref();
-    call->head_only = rq.method == Method::kHead;
-    call->close = conn.closing();
-    call->server_start_us = worker.loop().now_unix_us();
-    if (traced) {
-        call->server_ctx = start_server_trace(rq.b3, &st.ids);
-        call->server_url = "http://";
-        call->server_url.append(rq.host.empty() ? std::string_view("localhost") : rq.host);
-        call->server_url.append(rq.target);
-    }
+    const bool head_only = rq.method == Method::kHead;
+    const int64_t server_start_us = worker.loop().now_unix_us();
+    TraceContext server_ctx;
+    if (traced) server_ctx = start_server_trace(rq.b3, &st.ids);
+    const std::string_view url_host = rq.host.empty() ? std::string_view("localhost") : rq.host;
     if (!g.ok) {
         // hola() throws before the downstream call is attempted.
-        append_response(&conn.out(), 500, "text/html", undertow_error_page(500), false, conn.closing(), call->head_only,
-                        worker.http_date());
-        record_span(st, call->server_ctx, false, call->server_start_us, realtime_us(), 500, call->server_url, {}, {});
+        append_response(&conn.out(), 500, "text/html", undertow_error_page(500), false, conn.closing(), head_only, worker.http_date());
+        record_span(st, server_ctx, false, server_start_us, realtime_us(), 500, "http://", url_host, rq.target);
         return Disposition::kDone;
     }
-    call->hola_text = g.text;
+
+    const int64_t now_ms = worker.loop().now_ns() / 1000000;
+    const HystrixCommand::Admission adm = command_.admit(now_ms, worker.id());
+    if (adm != HystrixCommand::Admission::kRun) {
+        // Short-circuited (circuit open) or rejected (bulkhead full): straight to the fallback.
+        if (options_.verbose) {
+            std::fprintf(stderr, "hola: aloha call %s -> fallback\n",
+                         adm == HystrixCommand::Admission::kShortCircuited ? "short-circuited" : "rejected (pool full)");
+        }
+        int status = 200;
+        if (options_.breaker.fallback_enabled) {
+            append_fallback_response(st, conn, rq, g);
+        } else {
+            status = 500;
+            append_response(&conn.out(), 500, "text/html", undertow_error_page(500), false, conn.closing(), head_only, worker.http_date());
+        }
+        if (server_ctx.sampled) record_span(st, server_ctx, false, server_start_us, realtime_us(), status, "http://", url_host, rq.target);
+        return Disposition::kDone;
+    }
+
+    CallRef call = new_call(st);
+    call->greeting = st.greeting;
+    call->ref = conn.ref();
+    call->head_only = head_only;
+    call->close = conn.closing();
+    call->server_start_us = server_start_us;
+    call->server_ctx = server_ctx;
+    if (traced) {
+        call->server_url.assign("http://");
+        call->server_url.append(url_host);
+        call->server_url.append(rq.target);
+    }
     start_chain(st, call);
     if (call->finished) {
         conn.out().append(call->response);
@@ -54,29 +146,10 @@ Disposition HolaApp::serve_chaining(WorkerState& st, Connection& conn, const Req
     return Disposition::kDeferred;
 }
 
-// What a failed, timed-out, rejected or short-circuited call contributes to the response: the
-// static fallback list (HolaResource.java:112), or nothing when fallbacks are disabled.
-JsonStringList HolaApp::fallback_tail(ChainCall& call) const {
-    if (options_.breaker.fallback_enabled) return JsonStringList{options_.fallback};
-    call.failed_without_fallback = true;
-    return {};
-}
-
-void HolaApp::start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call) {
+// The breaker has admitted the call: arm the command timeout and send the first attempt.
+void HolaApp::start_chain(WorkerState& st, const CallRef& call) {
     EventLoop& loop = st.worker->loop();
-    const int64_t now_ms = loop.now_ns() / 1000000;
-    const HystrixCommand::Admission adm = command_.admit(now_ms);
-    if (adm != HystrixCommand::Admission::kRun) {
-        if (options_.verbose) {
-            std::fprintf(stderr, "hola: aloha call %s -> fallback\n",
-                         adm == HystrixCommand::Admission::kShortCircuited ? "short-circuited" : "rejected (pool full)");
-        }
-        call->settled = true;
-        finish_chain(st, call, fallback_tail(*call));
-        return;
-    }
     call->exec_start_ns = loop.now_ns();
-
     WorkerState* stp = &st;
     if (options_.breaker.timeout_enabled) {
         call->timer = loop.add_timer(
@@ -90,10 +163,10 @@ void HolaApp::start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& cal
                     call->retry_timer = 0;
                 }
                 stp->http->cancel(call->request);
-                command_.complete_timeout(lp.now_ns() / 1000000,
-                                          static_cast<int>((lp.now_ns() - call->exec_start_ns) / 1000000));
+                command_.complete_timeout(lp.now_ns() / 1000000, static_cast<int>((lp.now_ns() - call->exec_start_ns) / 1000000),
+                                          stp->worker->id());
                 if (options_.verbose) std::fprintf(stderr, "hola: aloha call timed out -> fallback\n");
-                finish_chain(*stp, call, fallback_tail(*call));
+                finish_chain(*stp, call, nullptr);
             });
     }
     send_chain_attempt(st, call);
@@ -105,7 +178,7 @@ void HolaApp::start_chain(WorkerState& st, const std::shared_ptr<ChainCall>& cal
 // 100 ms x 1.5^k (capped at 1 s) between them - all inside the one Hystrix command, so the
 // 600 ms command timeout is what usually ends a series of failing attempts. HTTP error statuses
 // and undecodable bodies are not retried.
-void HolaApp::send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCall>& call) {
+void HolaApp::send_chain_attempt(WorkerState& st, const CallRef& call) {
     ++call->attempt;
     call->client_ctx = start_client_trace(call->server_ctx, &st.ids);  // a fresh client span per attempt
     std::string request = aloha_request_prefix_;
@@ -122,11 +195,12 @@ void HolaApp::send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCal
     request.append("\r\n");
     call->client_start_us = realtime_us();
     WorkerState* stp = &st;
-    if (options_.verbose) std::fprintf(stderr, "[AlohaService#aloha] ---> GET %s HTTP/1.1\n", aloha_url_.c_str());
+    if (options_.log_feign) std::fprintf(stderr, "[AlohaService#aloha] ---> GET %s HTTP/1.1\n", aloha_url_.c_str());
     call->request = st.http->send(
         options_.aloha_host, options_.aloha_port, std::move(request), [this, stp, call](ClientResult&& r) {
             if (call->settled) return;
             EventLoop& lp = stp->worker->loop();
+            const int shard = stp->worker->id();
             const int64_t now_ns = monotonic_ns();
             const int exec_ms = static_cast<int>((now_ns - call->exec_start_ns) / 1000000);
             const bool io_failure = r.code == ClientResult::Code::kResolveFailed || r.code == ClientResult::Code::kConnectFailed ||
@@ -135,7 +209,7 @@ void HolaApp::send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCal
                 double interval_ms = options_.feign_retry_period_ms;
                 for (int k = 0; k < call->attempt; ++k) interval_ms *= 1.5;
                 if (interval_ms > options_.feign_retry_max_period_ms) interval_ms = options_.feign_retry_max_period_ms;
-                if (options_.verbose) {
+                if (options_.log_feign) {
                     std::fprintf(stderr, "[AlohaService#aloha] <--- ERROR %s (%dms)\n[AlohaService#aloha] ---> RETRYING in %.0f ms\n",
                                  r.describe(), exec_ms, interval_ms);
                 }
@@ -165,7 +239,7 @@ void HolaApp::send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCal
                     ok = true;
                 }
             }
-            if (options_.verbose) {
+            if (options_.log_feign) {
                 if (r.code == ClientResult::Code::kOk) {
                     std::fprintf(stderr, "[AlohaService#aloha] <--- HTTP/1.1 %d (%dms)\n", r.status, exec_ms);
                 } else {
@@ -173,41 +247,37 @@ void HolaApp::send_chain_attempt(WorkerState& st, const std::shared_ptr<ChainCal
                 }
             }
             if (ok) {
-                command_.complete_success(now_ns / 1000000, exec_ms);
-                finish_chain(*stp, call, std::move(tail));
+                command_.complete_success(now_ns / 1000000, exec_ms, shard);
+                finish_chain(*stp, call, &tail);
             } else {
-                command_.complete_failure(now_ns / 1000000, exec_ms);
-                finish_chain(*stp, call, fallback_tail(*call));
+                command_.complete_failure(now_ns / 1000000, exec_ms, shard);
+                finish_chain(*stp, call, nullptr);
             }
         });
 }
 
-void HolaApp::finish_chain(WorkerState& st, const std::shared_ptr<ChainCall>& call, JsonStringList&& tail) {
+void HolaApp::finish_chain(WorkerState& st, const CallRef& call, const JsonStringList* tail) {
     if (call->finished) return;
     call->finished = true;
     Worker& worker = *st.worker;
     const bool close = call->close || worker.draining();
-    std::string response;
+    std::string& response = call->response;
+    response.clear();
     int status = 200;
-    // An empty tail is the marker for "the call failed and fallbacks are switched off"
-    // (hystrix.command.default.fallback.enabled=false): Hystrix then throws, the resource method
-    // fails and the client sees a 500.
-    if (tail.empty() && call->failed_without_fallback) {
+    if (!tail && !options_.breaker.fallback_enabled) {
+        // hystrix.command.default.fallback.enabled=false: Hystrix throws, the resource method
+        // fails and the client sees a 500.
+        call->failed_without_fallback = true;
         status = 500;
         append_response(&response, 500, "text/html", undertow_error_page(500), false, close, call->head_only, worker.http_date());
     } else {
-        JsonStringList all;
-        all.reserve(tail.size() + 1);
-        all.emplace_back(std::move(call->hola_text));
-        for (auto& item : tail) all.emplace_back(std::move(item));
-        append_response(&response, 200, kJson, json_encode_string_list(all), true, close, call->head_only, worker.http_date());
+        st.scratch.clear();
+        append_chain_body(&st.scratch, call->greeting->text, tail);
+        append_response(&response, 200, kJson, st.scratch, true, close, call->head_only, worker.http_date());
     }
     record_span(st, call->server_ctx, false, call->server_start_us, realtime_us(), status, call->server_url, {}, {});
-    if (call->deferred) {
-        worker.complete(call->ref, response, close);
-    } else {
-        call->response = std::move(response);
-    }
+    if (call->deferred) worker.complete(call->ref, response, close);
+    // else: serve_chaining() is still on the stack and takes call->response itself
 }
 
 }  // namespace hola

@@ -50,6 +50,8 @@ std::string usage_text() {
            "                              for pinned, dedicated cores: trades idle CPU for lower latency)\n"
            "  --max-header-bytes N        request head limit (default 65536)\n"
            "  --log-config-reads          print the conf path on every config-file read, as the reference does\n"
+           "  --log-feign                 log every downstream call to stderr in Feign's BASIC format, as the reference does\n"
+           "  --reference-logging         both of the above: the log output of the Java service, for log scrapers\n"
            "  --serve-aloha               also answer GET /api/aloha-chaining with [\"Aloha mai <HOSTNAME>\"]: a stand-in\n"
            "                              for the next service of the demo chain (point another hola at it)\n"
            "  --print-greeting            print what GET /api/hola would answer with this configuration and exit\n"
@@ -162,6 +164,12 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
             cfg->log_config_reads = true;
         } else if (a == "--verbose") {
             cfg->app.verbose = true;
+            cfg->app.log_feign = true;
+        } else if (a == "--log-feign") {
+            cfg->app.log_feign = true;
+        } else if (a == "--reference-logging") {
+            cfg->app.log_feign = true;
+            cfg->log_config_reads = true;
         } else if (a == "--quiet") {
             cfg->quiet = true;
         } else if (a == "--serve-aloha") {

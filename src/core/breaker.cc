@@ -185,10 +185,14 @@ void RollingPercentile::add(int64_t now_ms, int value) {
     ++current_.next;
 }
 
-RollingPercentile::Snapshot RollingPercentile::snapshot(int64_t now_ms) {
+void RollingPercentile::collect(int64_t now_ms, std::vector<int>* out) {
     roll(now_ms);
+    for (const auto& b : closed_) out->insert(out->end(), b.samples.begin(), b.samples.end());
+}
+
+RollingPercentile::Snapshot RollingPercentile::make_snapshot(std::vector<int>&& samples) {
     Snapshot s;
-    for (const auto& b : closed_) s.sorted.insert(s.sorted.end(), b.samples.begin(), b.samples.end());
+    s.sorted = std::move(samples);
     std::sort(s.sorted.begin(), s.sorted.end());
     if (!s.sorted.empty()) {
         int64_t sum = 0;
@@ -196,6 +200,12 @@ RollingPercentile::Snapshot RollingPercentile::snapshot(int64_t now_ms) {
         s.mean = static_cast<int>(sum / static_cast<int64_t>(s.sorted.size()));
     }
     return s;
+}
+
+RollingPercentile::Snapshot RollingPercentile::snapshot(int64_t now_ms) {
+    std::vector<int> samples;
+    collect(now_ms, &samples);
+    return make_snapshot(std::move(samples));
 }
 
 int RollingPercentile::Snapshot::percentile(double pct) const {
@@ -213,154 +223,301 @@ int RollingPercentile::Snapshot::percentile(double pct) const {
 // ---------------------------------------------------------------------------------------------
 // HystrixCommand
 
+struct alignas(64) HystrixCommand::Shard {
+    explicit Shard(const BreakerConfig& cfg)
+        : health(cfg.health_interval_ms, std::max(1, cfg.rolling_window_ms / std::max(1, cfg.health_interval_ms))),
+          rolling(cfg.rolling_window_ms / std::max(1, cfg.rolling_buckets), cfg.rolling_buckets),
+          max_window(cfg.rolling_window_ms / std::max(1, cfg.rolling_buckets), cfg.rolling_buckets),
+          pool_window(cfg.rolling_window_ms / std::max(1, cfg.rolling_buckets), cfg.rolling_buckets),
+          latency_execute(cfg.percentile_window_ms, cfg.percentile_buckets, cfg.percentile_bucket_size),
+          latency_total(cfg.percentile_window_ms, cfg.percentile_buckets, cfg.percentile_bucket_size) {}
+
+    std::mutex mu;  // the owning thread on the request path; anybody when the shards are merged
+    int64_t health_origin_seen = kUnset;
+    RollingEventWindow health;
+    RollingEventWindow rolling;
+    RollingEventWindow max_window;   // slot kEmit: command concurrency, slot kSuccess: pool active
+    RollingEventWindow pool_window;  // slot kSuccess: executed, kThreadPoolRejected: rejected
+    std::array<int64_t, kHystrixEventCount> cumulative{};
+    RollingPercentile latency_execute;
+    RollingPercentile latency_total;
+    int64_t completed_tasks = 0;
+};
+
 HystrixCommand::HystrixCommand(std::string name, std::string group, std::string pool, const BreakerConfig& cfg)
-    : name_(std::move(name)),
-      group_(std::move(group)),
-      pool_(std::move(pool)),
-      cfg_(cfg),
-      health_window_(cfg.health_interval_ms, std::max(1, cfg.rolling_window_ms / std::max(1, cfg.health_interval_ms))),
-      rolling_window_(cfg.rolling_window_ms / std::max(1, cfg.rolling_buckets), cfg.rolling_buckets),
-      max_window_(cfg.rolling_window_ms / std::max(1, cfg.rolling_buckets), cfg.rolling_buckets),
-      pool_window_(cfg.rolling_window_ms / std::max(1, cfg.rolling_buckets), cfg.rolling_buckets),
-      latency_execute_(cfg.percentile_window_ms, cfg.percentile_buckets, cfg.percentile_bucket_size),
-      latency_total_(cfg.percentile_window_ms, cfg.percentile_buckets, cfg.percentile_bucket_size) {}
+    : name_(std::move(name)), group_(std::move(group)), pool_(std::move(pool)), cfg_(cfg) {}
+
+HystrixCommand::HystrixCommand(HystrixCommand&& o) noexcept
+    : name_(std::move(o.name_)), group_(std::move(o.group_)), pool_(std::move(o.pool_)), cfg_(o.cfg_) {
+    circuit_open_.store(o.circuit_open_.load());
+    opened_or_tested_ms_.store(o.opened_or_tested_ms_.load());
+    active_.store(o.active_.load());
+    largest_active_.store(o.largest_active_.load());
+    executed_once_.store(o.executed_once_.load());
+    origin_ms_.store(o.origin_ms_.load());
+    health_origin_ms_.store(o.health_origin_ms_.load());
+    evaluated_bucket_.store(o.evaluated_bucket_.load());
+    for (int i = 0; i < kMaxShards; ++i) shards_[static_cast<size_t>(i)].store(o.shards_[static_cast<size_t>(i)].exchange(nullptr));
+}
+
+HystrixCommand::~HystrixCommand() {
+    for (auto& s : shards_) delete s.load(std::memory_order_relaxed);
+}
+
+HystrixCommand::Shard& HystrixCommand::shard(int index) {
+    std::atomic<Shard*>& slot = shards_[static_cast<size_t>(static_cast<unsigned>(index) % kMaxShards)];
+    Shard* s = slot.load(std::memory_order_acquire);
+    if (s) return *s;
+    std::lock_guard<std::mutex> lock(mu_);
+    s = slot.load(std::memory_order_relaxed);
+    if (!s) {
+        s = new Shard(cfg_);
+        slot.store(s, std::memory_order_release);
+    }
+    return *s;
+}
+
+void HystrixCommand::touch(int64_t now_ms) {
+    if (origin_ms_.load(std::memory_order_relaxed) != kUnset) return;
+    int64_t expected = kUnset;
+    if (origin_ms_.compare_exchange_strong(expected, now_ms, std::memory_order_relaxed)) {
+        expected = kUnset;
+        health_origin_ms_.compare_exchange_strong(expected, now_ms, std::memory_order_release);
+    } else {
+        // Another thread is fixing the origin this very moment; wait for the second store.
+        while (health_origin_ms_.load(std::memory_order_acquire) == kUnset) {
+        }
+    }
+}
+
+// A shard's health window follows the command's health origin: when the origin has moved (the
+// circuit closed and the history was wiped) the shard's window is wiped the next time it is used.
+// Two wipes cannot fall into the same millisecond - re-opening takes at least one closed bucket -
+// so the origin identifies the wipe.
+void HystrixCommand::sync_health(Shard& s) {
+    const int64_t origin = health_origin_ms_.load(std::memory_order_acquire);
+    if (s.health_origin_seen != origin) {
+        s.health.reset(origin);
+        s.health_origin_seen = origin;
+    }
+}
+
+void HystrixCommand::record(Shard& s, int64_t now_ms, HystrixEvent e) {
+    sync_health(s);
+    s.health.add(now_ms, e);
+    s.rolling.start_at(origin_ms_.load(std::memory_order_relaxed));
+    s.rolling.add(now_ms, e);
+    ++s.cumulative[static_cast<size_t>(e)];
+}
 
 HealthCounts HystrixCommand::health_locked(int64_t now_ms) {
     HealthCounts h;
-    const int64_t success = health_window_.sum(now_ms, HystrixEvent::kSuccess);
-    h.errors = health_window_.sum(now_ms, HystrixEvent::kFailure) + health_window_.sum(now_ms, HystrixEvent::kTimeout) +
-               health_window_.sum(now_ms, HystrixEvent::kThreadPoolRejected) +
-               health_window_.sum(now_ms, HystrixEvent::kSemaphoreRejected);
+    int64_t success = 0;
+    for (auto& slot : shards_) {
+        Shard* s = slot.load(std::memory_order_acquire);
+        if (!s) continue;
+        std::lock_guard<std::mutex> lock(s->mu);
+        sync_health(*s);
+        success += s->health.sum(now_ms, HystrixEvent::kSuccess);
+        h.errors += s->health.sum(now_ms, HystrixEvent::kFailure) + s->health.sum(now_ms, HystrixEvent::kTimeout) +
+                    s->health.sum(now_ms, HystrixEvent::kThreadPoolRejected) +
+                    s->health.sum(now_ms, HystrixEvent::kSemaphoreRejected);
+    }
     h.total = success + h.errors;
     h.error_pct = h.total > 0 ? static_cast<int>(static_cast<double>(h.errors) / static_cast<double>(h.total) * 100.0) : 0;
     return h;
 }
 
-bool HystrixCommand::is_open_locked(int64_t now_ms) {
-    if (circuit_open_) return true;
+bool HystrixCommand::evaluate_open_locked(int64_t now_ms) {
+    if (circuit_open_.load(std::memory_order_relaxed)) return true;
     const HealthCounts h = health_locked(now_ms);
-    if (h.total < cfg_.request_volume_threshold) return false;
-    if (h.error_pct < cfg_.error_threshold_pct) return false;
-    circuit_open_ = true;
-    opened_or_tested_ms_ = now_ms;
-    return true;
-}
-
-bool HystrixCommand::allow_request_locked(int64_t now_ms) {
-    if (!cfg_.breaker_enabled) return true;
-    if (cfg_.force_open) return false;
-    if (cfg_.force_closed) {
-        is_open_locked(now_ms);  // keeps the open flag current for the metrics, as Hystrix does
+    if (h.total >= cfg_.request_volume_threshold && h.error_pct >= cfg_.error_threshold_pct) {
+        opened_or_tested_ms_.store(now_ms, std::memory_order_relaxed);
+        circuit_open_.store(true, std::memory_order_release);
         return true;
     }
-    if (!is_open_locked(now_ms)) return true;
-    // Open: let one trial call through per sleep window.
-    if (now_ms > opened_or_tested_ms_ + cfg_.sleep_window_ms) {
-        opened_or_tested_ms_ = now_ms;
-        return true;
+    // Closed, and it stays closed until another health bucket closes: only closed buckets count.
+    const int64_t origin = health_origin_ms_.load(std::memory_order_relaxed);
+    const int64_t bucket = (now_ms - origin) / std::max(1, cfg_.health_interval_ms);
+    if (bucket > evaluated_bucket_.load(std::memory_order_relaxed)) evaluated_bucket_.store(bucket, std::memory_order_relaxed);
+    return false;
+}
+
+void HystrixCommand::reset_health_locked(int64_t now_ms) {
+    evaluated_bucket_.store(-1, std::memory_order_relaxed);
+    health_origin_ms_.store(now_ms, std::memory_order_release);
+}
+
+bool HystrixCommand::allow_request(int64_t now_ms) {
+    if (!cfg_.breaker_enabled) return true;
+    if (cfg_.force_open) return false;
+    bool open = circuit_open_.load(std::memory_order_acquire);
+    if (!open) {
+        const int64_t origin = health_origin_ms_.load(std::memory_order_relaxed);
+        const int64_t bucket = (now_ms - origin) / std::max(1, cfg_.health_interval_ms);
+        if (bucket > evaluated_bucket_.load(std::memory_order_relaxed)) {
+            std::lock_guard<std::mutex> lock(mu_);
+            open = evaluate_open_locked(now_ms);
+        }
+    }
+    if (cfg_.force_closed) return true;  // the open flag is still kept current for the metrics, as Hystrix does
+    if (!open) return true;
+    // Open: let one trial call through per sleep window; whoever moves the time stamp gets it.
+    int64_t tested = opened_or_tested_ms_.load(std::memory_order_relaxed);
+    while (now_ms > tested + cfg_.sleep_window_ms) {
+        if (opened_or_tested_ms_.compare_exchange_weak(tested, now_ms, std::memory_order_relaxed)) return true;
     }
     return false;
 }
 
-void HystrixCommand::record_locked(int64_t now_ms, HystrixEvent e) {
-    health_window_.add(now_ms, e);
-    rolling_window_.add(now_ms, e);
-    ++cumulative_[static_cast<size_t>(e)];
-}
-
-HystrixCommand::Admission HystrixCommand::admit(int64_t now_ms) {
-    std::lock_guard<std::mutex> lock(mu_);
-    executed_once_.store(true, std::memory_order_relaxed);
-    if (!allow_request_locked(now_ms)) {
-        record_locked(now_ms, HystrixEvent::kShortCircuited);
-        record_locked(now_ms, cfg_.fallback_enabled ? HystrixEvent::kFallbackSuccess : HystrixEvent::kFallbackMissing);
-        latency_total_.add(now_ms, 0);
+HystrixCommand::Admission HystrixCommand::admit(int64_t now_ms, int shard_index) {
+    touch(now_ms);
+    if (!executed_once_.load(std::memory_order_relaxed)) executed_once_.store(true, std::memory_order_relaxed);
+    Shard& s = shard(shard_index);
+    const HystrixEvent fallback = cfg_.fallback_enabled ? HystrixEvent::kFallbackSuccess : HystrixEvent::kFallbackMissing;
+    if (!allow_request(now_ms)) {
+        std::lock_guard<std::mutex> lock(s.mu);
+        record(s, now_ms, HystrixEvent::kShortCircuited);
+        record(s, now_ms, fallback);
+        s.latency_total.start_at(origin_ms_.load(std::memory_order_relaxed));
+        s.latency_total.add(now_ms, 0);
         return Admission::kShortCircuited;
     }
-    if (active_ >= cfg_.pool_core_size) {
-        record_locked(now_ms, HystrixEvent::kThreadPoolRejected);
-        record_locked(now_ms, cfg_.fallback_enabled ? HystrixEvent::kFallbackSuccess : HystrixEvent::kFallbackMissing);
-        pool_window_.add(now_ms, HystrixEvent::kThreadPoolRejected);
-        latency_total_.add(now_ms, 0);
+    // Take a slot of the bulkhead, if there is one (never counting past its size, not even
+    // for a moment: the count is what the metrics stream shows).
+    int running = active_.load(std::memory_order_relaxed);
+    while (running < cfg_.pool_core_size && !active_.compare_exchange_weak(running, running + 1, std::memory_order_acq_rel)) {
+    }
+    if (running >= cfg_.pool_core_size) {
+        std::lock_guard<std::mutex> lock(s.mu);
+        record(s, now_ms, HystrixEvent::kThreadPoolRejected);
+        record(s, now_ms, fallback);
+        s.pool_window.start_at(origin_ms_.load(std::memory_order_relaxed));
+        s.pool_window.add(now_ms, HystrixEvent::kThreadPoolRejected);
+        s.latency_total.start_at(origin_ms_.load(std::memory_order_relaxed));
+        s.latency_total.add(now_ms, 0);
         return Admission::kPoolRejected;
     }
-    ++active_;
-    largest_active_ = std::max(largest_active_, active_);
-    max_window_.update_max(now_ms, HystrixEvent::kEmit, active_);
-    max_window_.update_max(now_ms, HystrixEvent::kSuccess, active_);
-    pool_window_.add(now_ms, HystrixEvent::kSuccess);
+    const int now_running = running + 1;
+    int largest = largest_active_.load(std::memory_order_relaxed);
+    while (now_running > largest && !largest_active_.compare_exchange_weak(largest, now_running, std::memory_order_relaxed)) {
+    }
+    std::lock_guard<std::mutex> lock(s.mu);
+    const int64_t origin = origin_ms_.load(std::memory_order_relaxed);
+    s.max_window.start_at(origin);
+    s.max_window.update_max(now_ms, HystrixEvent::kEmit, now_running);
+    s.max_window.update_max(now_ms, HystrixEvent::kSuccess, now_running);
+    s.pool_window.start_at(origin);
+    s.pool_window.add(now_ms, HystrixEvent::kSuccess);
     return Admission::kRun;
 }
 
-void HystrixCommand::finish_locked(int64_t now_ms, HystrixEvent e, int execute_ms) {
-    if (active_ > 0) --active_;
-    ++completed_tasks_;
-    record_locked(now_ms, e);
+void HystrixCommand::finish(int64_t now_ms, HystrixEvent e, int execute_ms, int shard_index) {
+    touch(now_ms);
+    int running = active_.load(std::memory_order_relaxed);
+    while (running > 0 && !active_.compare_exchange_weak(running, running - 1, std::memory_order_acq_rel)) {
+    }
+    Shard& s = shard(shard_index);
+    std::lock_guard<std::mutex> lock(s.mu);
+    ++s.completed_tasks;
+    record(s, now_ms, e);
     if (e != HystrixEvent::kSuccess)
-        record_locked(now_ms, cfg_.fallback_enabled ? HystrixEvent::kFallbackSuccess : HystrixEvent::kFallbackMissing);
-    latency_execute_.add(now_ms, execute_ms);
-    latency_total_.add(now_ms, execute_ms);
+        record(s, now_ms, cfg_.fallback_enabled ? HystrixEvent::kFallbackSuccess : HystrixEvent::kFallbackMissing);
+    const int64_t origin = origin_ms_.load(std::memory_order_relaxed);
+    s.latency_execute.start_at(origin);
+    s.latency_execute.add(now_ms, execute_ms);
+    s.latency_total.start_at(origin);
+    s.latency_total.add(now_ms, execute_ms);
 }
 
-void HystrixCommand::complete_success(int64_t now_ms, int execute_ms) {
-    std::lock_guard<std::mutex> lock(mu_);
-    finish_locked(now_ms, HystrixEvent::kSuccess, execute_ms);
-    if (circuit_open_) {
-        circuit_open_ = false;
-        health_window_.reset(now_ms);
+void HystrixCommand::complete_success(int64_t now_ms, int execute_ms, int shard_index) {
+    finish(now_ms, HystrixEvent::kSuccess, execute_ms, shard_index);
+    if (circuit_open_.load(std::memory_order_acquire)) {
+        // The trial call (or a straggler from before the trip) came back fine: close the circuit
+        // and forget the history, this success included.
+        std::lock_guard<std::mutex> lock(mu_);
+        if (circuit_open_.load(std::memory_order_relaxed)) {
+            reset_health_locked(now_ms);
+            circuit_open_.store(false, std::memory_order_release);
+        }
     }
 }
 
-void HystrixCommand::complete_failure(int64_t now_ms, int execute_ms) {
-    std::lock_guard<std::mutex> lock(mu_);
-    finish_locked(now_ms, HystrixEvent::kFailure, execute_ms);
+void HystrixCommand::complete_failure(int64_t now_ms, int execute_ms, int shard_index) {
+    finish(now_ms, HystrixEvent::kFailure, execute_ms, shard_index);
 }
 
-void HystrixCommand::complete_timeout(int64_t now_ms, int execute_ms) {
-    std::lock_guard<std::mutex> lock(mu_);
-    finish_locked(now_ms, HystrixEvent::kTimeout, execute_ms);
+void HystrixCommand::complete_timeout(int64_t now_ms, int execute_ms, int shard_index) {
+    finish(now_ms, HystrixEvent::kTimeout, execute_ms, shard_index);
 }
 
 bool HystrixCommand::is_open(int64_t now_ms) {
-    std::lock_guard<std::mutex> lock(mu_);
+    touch(now_ms);
     if (!cfg_.breaker_enabled) return false;
     if (cfg_.force_open) return true;
-    return is_open_locked(now_ms);
+    std::lock_guard<std::mutex> lock(mu_);
+    return evaluate_open_locked(now_ms);
 }
 
 HealthCounts HystrixCommand::health(int64_t now_ms) {
+    touch(now_ms);
     std::lock_guard<std::mutex> lock(mu_);
     return health_locked(now_ms);
 }
 
 CommandSnapshot HystrixCommand::snapshot(int64_t now_ms) {
-    std::lock_guard<std::mutex> lock(mu_);
-    CommandSnapshot s;
-    s.now_ms = now_ms;
-    s.circuit_open = cfg_.breaker_enabled && (cfg_.force_open || (!cfg_.force_closed && is_open_locked(now_ms)));
-    s.health = health_locked(now_ms);
-    for (int i = 0; i < kHystrixEventCount; ++i)
-        s.rolling[static_cast<size_t>(i)] = rolling_window_.sum(now_ms, static_cast<HystrixEvent>(i));
-    s.cumulative = cumulative_;
-    s.current_concurrent = active_;
-    s.rolling_max_concurrent = max_window_.max(now_ms, HystrixEvent::kEmit);
-    s.latency_execute = latency_execute_.snapshot(now_ms);
-    s.latency_total = latency_total_.snapshot(now_ms);
-    return s;
+    touch(now_ms);
+    CommandSnapshot out;
+    out.now_ms = now_ms;
+    {
+        std::lock_guard<std::mutex> lock(mu_);
+        out.circuit_open = cfg_.breaker_enabled && (cfg_.force_open || (!cfg_.force_closed && evaluate_open_locked(now_ms)));
+        out.health = health_locked(now_ms);
+    }
+    const int64_t origin = origin_ms_.load(std::memory_order_relaxed);
+    std::vector<int> execute_samples, total_samples;
+    for (auto& slot : shards_) {
+        Shard* s = slot.load(std::memory_order_acquire);
+        if (!s) continue;
+        std::lock_guard<std::mutex> lock(s->mu);
+        s->rolling.start_at(origin);
+        s->max_window.start_at(origin);
+        s->latency_execute.start_at(origin);
+        s->latency_total.start_at(origin);
+        for (int i = 0; i < kHystrixEventCount; ++i) {
+            out.rolling[static_cast<size_t>(i)] += s->rolling.sum(now_ms, static_cast<HystrixEvent>(i));
+            out.cumulative[static_cast<size_t>(i)] += s->cumulative[static_cast<size_t>(i)];
+        }
+        out.rolling_max_concurrent = std::max(out.rolling_max_concurrent, s->max_window.max(now_ms, HystrixEvent::kEmit));
+        s->latency_execute.collect(now_ms, &execute_samples);
+        s->latency_total.collect(now_ms, &total_samples);
+    }
+    out.current_concurrent = active_.load(std::memory_order_relaxed);
+    out.latency_execute = RollingPercentile::make_snapshot(std::move(execute_samples));
+    out.latency_total = RollingPercentile::make_snapshot(std::move(total_samples));
+    return out;
 }
 
 PoolSnapshot HystrixCommand::pool_snapshot(int64_t now_ms) {
-    std::lock_guard<std::mutex> lock(mu_);
+    touch(now_ms);
     PoolSnapshot p;
     p.now_ms = now_ms;
-    p.active = active_;
-    p.completed_tasks = completed_tasks_;
-    p.task_count = completed_tasks_ + active_;
-    p.largest_pool_size = largest_active_;
-    p.pool_size = std::min(cfg_.pool_core_size, largest_active_);
-    p.rolling_executed = pool_window_.sum(now_ms, HystrixEvent::kSuccess);
-    p.rolling_rejected = pool_window_.sum(now_ms, HystrixEvent::kThreadPoolRejected);
-    p.rolling_max_active = max_window_.max(now_ms, HystrixEvent::kSuccess);
+    const int64_t origin = origin_ms_.load(std::memory_order_relaxed);
+    for (auto& slot : shards_) {
+        Shard* s = slot.load(std::memory_order_acquire);
+        if (!s) continue;
+        std::lock_guard<std::mutex> lock(s->mu);
+        s->pool_window.start_at(origin);
+        s->max_window.start_at(origin);
+        p.completed_tasks += s->completed_tasks;
+        p.rolling_executed += s->pool_window.sum(now_ms, HystrixEvent::kSuccess);
+        p.rolling_rejected += s->pool_window.sum(now_ms, HystrixEvent::kThreadPoolRejected);
+        p.rolling_max_active = std::max(p.rolling_max_active, s->max_window.max(now_ms, HystrixEvent::kSuccess));
+    }
+    p.active = active_.load(std::memory_order_relaxed);
+    p.task_count = p.completed_tasks + p.active;
+    p.largest_pool_size = largest_active_.load(std::memory_order_relaxed);
+    p.pool_size = std::min(cfg_.pool_core_size, p.largest_pool_size);
     return p;
 }
 

@@ -20,6 +20,18 @@
 //
 // The class is clock-agnostic: every method takes "now" in milliseconds, which lets the unit
 // tests drive the state machine with a synthetic clock. All methods are thread-safe.
+//
+// Concurrency. Hystrix keeps one set of counters per command and every request thread writes to
+// it; here the request path must not meet another core's cache lines, let alone a shared lock.
+// Counters are therefore kept in *shards* - one per event-loop thread, each behind its own mutex
+// that only its owner takes on the request path - and merged when somebody looks (the metrics
+// stream, the trip decision). What is shared is small and lock-free: the open flag, the time of
+// the last trial (one compare-and-swap decides who gets the single trial per sleep window) and
+// the bulkhead's count of running calls. The trip decision itself depends only on *closed* health
+// buckets, so it is re-evaluated once per health interval (500 ms) - under the command's lock,
+// merging the shards - and not on every call. All shards cut their buckets at the same instants
+// (a shared origin), which makes the merged window identical to the single window it replaces:
+// for any single-threaded sequence of calls the behaviour is exactly what it was.
 #pragma once
 
 #include <array>
@@ -98,6 +110,11 @@ class RollingEventWindow {
     int64_t sum(int64_t now_ms, HystrixEvent e);
     int64_t max(int64_t now_ms, HystrixEvent slot);
     void reset(int64_t now_ms);
+    // Starts the window with its first bucket beginning at `origin_ms` unless it is running
+    // already (an unstarted window otherwise starts at the time of its first use).
+    void start_at(int64_t origin_ms) {
+        if (!started_) reset(origin_ms);
+    }
 
  private:
     using Bucket = std::array<int64_t, kHystrixEventCount>;
@@ -123,6 +140,15 @@ class RollingPercentile {
         int percentile(double pct) const;
     };
     Snapshot snapshot(int64_t now_ms);
+    // Appends the samples of the closed buckets to *out (for merging several reservoirs).
+    void collect(int64_t now_ms, std::vector<int>* out);
+    static Snapshot make_snapshot(std::vector<int>&& samples);
+    void start_at(int64_t origin_ms) {
+        if (!started_) {
+            started_ = true;
+            current_start_ = origin_ms;
+        }
+    }
 
  private:
     struct Bucket {
@@ -174,7 +200,13 @@ struct PoolSnapshot {
 // One command key + its thread pool, as a single unit (the reference has exactly one of each).
 class HystrixCommand {
  public:
+    static constexpr int kMaxShards = 64;
+
     HystrixCommand(std::string name, std::string group, std::string pool, const BreakerConfig& cfg);
+    ~HystrixCommand();
+    HystrixCommand(HystrixCommand&& other) noexcept;  // for factory functions; not while in use
+    HystrixCommand(const HystrixCommand&) = delete;
+    HystrixCommand& operator=(const HystrixCommand&) = delete;
 
     const std::string& name() const { return name_; }
     const std::string& group() const { return group_; }
@@ -183,17 +215,21 @@ class HystrixCommand {
 
     enum class Admission { kRun, kShortCircuited, kPoolRejected };
 
+    // `shard` in every call below: which set of counters the event is booked to. Pass the index
+    // of the calling event-loop thread (any value works - it is taken modulo kMaxShards - but
+    // two threads that share a shard share its lock).
+
     // Decides whether a call may run. kRun reserves a pool slot that must be given back with
     // exactly one of complete_*(). The two rejections record their events (including the
     // successful fallback, when fallbacks are enabled) and need no further call.
-    Admission admit(int64_t now_ms);
+    Admission admit(int64_t now_ms, int shard = 0);
 
     // Outcomes of an admitted call. `execute_ms` is the time spent in the call itself.
-    void complete_success(int64_t now_ms, int execute_ms);
-    void complete_failure(int64_t now_ms, int execute_ms);
-    void complete_timeout(int64_t now_ms, int execute_ms);
+    void complete_success(int64_t now_ms, int execute_ms, int shard = 0);
+    void complete_failure(int64_t now_ms, int execute_ms, int shard = 0);
+    void complete_timeout(int64_t now_ms, int execute_ms, int shard = 0);
 
-    // Pure views of the state machine, for tests and the metrics stream.
+    // Views of the state machine, for tests and the metrics stream (they merge the shards).
     bool is_open(int64_t now_ms);
     HealthCounts health(int64_t now_ms);
     CommandSnapshot snapshot(int64_t now_ms);
@@ -201,28 +237,34 @@ class HystrixCommand {
     bool has_executed() const { return executed_once_.load(std::memory_order_relaxed); }
 
  private:
-    bool allow_request_locked(int64_t now_ms);
-    bool is_open_locked(int64_t now_ms);
-    HealthCounts health_locked(int64_t now_ms);
-    void record_locked(int64_t now_ms, HystrixEvent e);
-    void finish_locked(int64_t now_ms, HystrixEvent e, int execute_ms);
+    struct Shard;
+    static constexpr int64_t kUnset = INT64_MIN;
 
-    const std::string name_, group_, pool_;
-    const BreakerConfig cfg_;
-    std::mutex mu_;
-    bool circuit_open_ = false;
-    int64_t opened_or_tested_ms_ = 0;
-    RollingEventWindow health_window_;
-    RollingEventWindow rolling_window_;
-    RollingEventWindow max_window_;       // slot kEmit: command concurrency, slot kSuccess: pool active
-    RollingEventWindow pool_window_;      // slot kSuccess: executed, kThreadPoolRejected: rejected
-    std::array<int64_t, kHystrixEventCount> cumulative_{};
-    RollingPercentile latency_execute_;
-    RollingPercentile latency_total_;
-    int active_ = 0;
-    int largest_active_ = 0;
-    int64_t completed_tasks_ = 0;
-    std::atomic<bool> executed_once_{false};  // read by the metrics stream without the lock
+    Shard& shard(int index);
+    void touch(int64_t now_ms);                      // fixes the windows' origin at the first use of the command
+    void sync_health(Shard& s);                      // s.mu held: applies a pending reset of the health window
+    void record(Shard& s, int64_t now_ms, HystrixEvent e);  // s.mu held
+    void finish(int64_t now_ms, HystrixEvent e, int execute_ms, int shard);
+    bool allow_request(int64_t now_ms);
+    bool evaluate_open_locked(int64_t now_ms);       // mu_ held: the trip decision on the merged health counts
+    HealthCounts health_locked(int64_t now_ms);      // mu_ held
+    void reset_health_locked(int64_t now_ms);        // mu_ held
+
+    std::string name_, group_, pool_;
+    BreakerConfig cfg_;
+
+    // Shared and lock-free on the request path.
+    std::atomic<bool> circuit_open_{false};
+    std::atomic<int64_t> opened_or_tested_ms_{0};
+    std::atomic<int> active_{0};
+    std::atomic<int> largest_active_{0};
+    std::atomic<bool> executed_once_{false};
+    std::atomic<int64_t> origin_ms_{kUnset};          // bucket alignment of the rolling windows
+    std::atomic<int64_t> health_origin_ms_{kUnset};   // ... of the health windows (moves when the circuit closes)
+    std::atomic<int64_t> evaluated_bucket_{-1};       // last health bucket for which "stays closed" was established
+
+    std::mutex mu_;  // trip evaluation, health reset, shard creation
+    std::array<std::atomic<Shard*>, kMaxShards> shards_{};
 };
 
 // Rendering of the two `data:` payloads of /hystrix.stream with Hystrix 1.5.1's field names.

@@ -1,5 +1,8 @@
 // Circuit-breaker state machine driven by a synthetic clock.
+#include <atomic>
 #include <string>
+#include <thread>
+#include <vector>
 
 #include "core/breaker.h"
 #include "testing.h"
@@ -190,4 +193,111 @@ TEST(rolling_percentile) {
     CHECK_EQ(s.percentile(50), 51);
     CHECK_EQ(s.percentile(100), 100);
     CHECK_EQ(p.snapshot(80000).sorted.size(), size_t{0});  // aged out
+}
+
+// The same schedule of calls booked to one shard and spread over many shards must be
+// indistinguishable: shards cut their buckets at the same instants, so the merged window is the
+// single window.
+TEST(breaker_shards_merge_to_the_same_state_machine) {
+    uint64_t rng = 0x9E3779B97F4A7C15ull;
+    auto next = [&rng] {
+        rng ^= rng << 13;
+        rng ^= rng >> 7;
+        rng ^= rng << 17;
+        return rng;
+    };
+    for (int round = 0; round < 50; ++round) {
+        HystrixCommand one = make(), many = make();
+        int64_t now = 5000;
+        struct Pending { int64_t due; int outcome; int shard; };
+        std::vector<Pending> pending;
+        for (int step = 0; step < 120; ++step) {
+            now += static_cast<int64_t>(next() % 400);
+            for (size_t i = 0; i < pending.size();) {
+                if (pending[i].due <= now) {
+                    const Pending p = pending[i];
+                    pending.erase(pending.begin() + static_cast<long>(i));
+                    if (p.outcome == 0) { one.complete_success(now, 3); many.complete_success(now, 3, p.shard); }
+                    else if (p.outcome == 1) { one.complete_failure(now, 3); many.complete_failure(now, 3, p.shard); }
+                    else { one.complete_timeout(now, 600); many.complete_timeout(now, 600, p.shard); }
+                } else {
+                    ++i;
+                }
+            }
+            const int shard = static_cast<int>(next() % 7);
+            const auto a = one.admit(now), b = many.admit(now, shard);
+            CHECK(a == b);
+            if (a == HystrixCommand::Admission::kRun) {
+                pending.push_back(Pending{now + static_cast<int64_t>(next() % 900), static_cast<int>(next() % 4 == 0 ? 0 : 1 + next() % 2), shard});
+            }
+            CHECK_EQ(one.is_open(now), many.is_open(now));
+            const HealthCounts h1 = one.health(now), h2 = many.health(now);
+            CHECK_EQ(h1.total, h2.total);
+            CHECK_EQ(h1.errors, h2.errors);
+        }
+        const CommandSnapshot s1 = one.snapshot(now + 1000), s2 = many.snapshot(now + 1000);
+        for (int e = 0; e < kHystrixEventCount; ++e) {
+            CHECK_EQ(s1.rolling[static_cast<size_t>(e)], s2.rolling[static_cast<size_t>(e)]);
+            CHECK_EQ(s1.cumulative[static_cast<size_t>(e)], s2.cumulative[static_cast<size_t>(e)]);
+        }
+        CHECK_EQ(s1.rolling_max_concurrent, s2.rolling_max_concurrent);
+        CHECK_EQ(s1.latency_total.sorted.size(), s2.latency_total.sorted.size());
+        const PoolSnapshot p1 = one.pool_snapshot(now + 1000), p2 = many.pool_snapshot(now + 1000);
+        CHECK_EQ(p1.rolling_executed, p2.rolling_executed);
+        CHECK_EQ(p1.rolling_rejected, p2.rolling_rejected);
+        CHECK_EQ(p1.completed_tasks, p2.completed_tasks);
+        CHECK_EQ(p1.rolling_max_active, p2.rolling_max_active);
+    }
+}
+
+// Eight threads, each on its own shard, against one command while a ninth takes snapshots: totals
+// must add up and the bulkhead must never admit more than its size (run under TSan by `make tsan`).
+TEST(breaker_concurrent_shards) {
+    BreakerConfig cfg = BreakerConfig::reference_defaults();
+    cfg.force_closed = true;  // keep admitting; the trip logic is exercised by the other tests
+    cfg.pool_core_size = 4;
+    HystrixCommand c = make(cfg);
+    constexpr int kThreads = 8, kCalls = 20000;
+    std::atomic<int> running{0}, max_running{0}, admitted{0}, rejected{0};
+    std::atomic<bool> stop{false};
+    std::thread watcher([&] {
+        int64_t t = 1000;
+        while (!stop.load()) {
+            const CommandSnapshot s = c.snapshot(t);
+            CHECK(s.current_concurrent >= 0 && s.current_concurrent <= 4);
+            c.pool_snapshot(t);
+            c.is_open(t);
+            t += 7;
+        }
+    });
+    std::vector<std::thread> threads;
+    for (int k = 0; k < kThreads; ++k) {
+        threads.emplace_back([&, k] {
+            for (int i = 0; i < kCalls; ++i) {
+                const int64_t now = 1000 + i / 10;
+                if (c.admit(now, k) == HystrixCommand::Admission::kRun) {
+                    const int r = running.fetch_add(1) + 1;
+                    int m = max_running.load();
+                    while (r > m && !max_running.compare_exchange_weak(m, r)) {
+                    }
+                    admitted.fetch_add(1);
+                    running.fetch_sub(1);
+                    if (i % 3 == 0) c.complete_failure(now, 1, k); else c.complete_success(now, 1, k);
+                } else {
+                    rejected.fetch_add(1);
+                }
+            }
+        });
+    }
+    for (auto& t : threads) t.join();
+    stop.store(true);
+    watcher.join();
+    CHECK(max_running.load() <= 4);
+    CHECK_EQ(admitted.load() + rejected.load(), kThreads * kCalls);
+    const CommandSnapshot s = c.snapshot(1000 + kCalls / 10 + 20000);
+    const auto cum = [&](HystrixEvent e) { return s.cumulative[static_cast<size_t>(e)]; };
+    CHECK_EQ(cum(HystrixEvent::kSuccess) + cum(HystrixEvent::kFailure), static_cast<int64_t>(admitted.load()));
+    CHECK_EQ(cum(HystrixEvent::kThreadPoolRejected), static_cast<int64_t>(rejected.load()));
+    CHECK_EQ(s.current_concurrent, 0);
+    CHECK_EQ(c.pool_snapshot(1).completed_tasks, static_cast<int64_t>(admitted.load()));
 }

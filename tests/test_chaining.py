@@ -255,3 +255,32 @@ def test_head_on_chaining(hola_server, fake_aloha):
     srv = hola_server(args=["--aloha-url", fake_aloha.url])
     r = client.get("127.0.0.1", srv.port, "/api/hola-chaining", method="HEAD")
     assert r.status == 200 and r.body == b"" and int(r.header("Content-Length")) > 20
+
+
+def test_chaining_under_load_on_every_outcome(hola_server):
+    """Many workers, many connections, all three outcomes of the downstream call one after the
+    other - success against a second hola that plays `aloha`, then a dead downstream (failures
+    until the circuit opens, short-circuits afterwards) - with a metrics-stream subscriber merging
+    the per-worker counters meanwhile. No request may fail; run with --variant tsan to have
+    ThreadSanitizer watch the sharded breaker and the pooled call objects."""
+    from hola_b200 import loadgen
+    aloha = hola_server(args=["--serve-aloha"], env={"HOSTNAME": "next"}, threads=2)
+    srv = hola_server(args=["--aloha-url", aloha.base_url + "/", "-Dhystrix.threadpool.default.coreSize=64"], threads=4)
+    stream = client.Connection("127.0.0.1", srv.port)
+    stream.send_raw(client.build_request("GET", "/hystrix.stream?delay=20"))
+    rep = loadgen.run(srv.base_url + "/api/hola-chaining", connections=32, duration=1.0, warmup=0.2, interval=0.5, threads=2,
+                      expect_body=b'["Hola de unknown","Aloha mai next"]')
+    assert rep["errors"]["total"] == 0 and rep["requests"] > 200
+    assert min(w["requests"] for w in srv.stats()["workers"]) > 0
+    stream.close()
+    # A dead downstream, on a fresh instance (the thousands of successes above would keep the
+    # error percentage of this one far below 50 % for the next ten seconds).
+    dead = hola_server(args=["--aloha-url", "http://127.0.0.1:9/", "--feign-max-attempts", "1"], threads=4)
+    stream = client.Connection("127.0.0.1", dead.port)
+    stream.send_raw(client.build_request("GET", "/hystrix.stream?delay=20"))
+    fallback = b'["Hola de unknown","Aloha response (fallback)"]'
+    rep = loadgen.run(dead.base_url + "/api/hola-chaining", connections=32, duration=2.0, warmup=0.2, interval=0.5, threads=2,
+                      expect_body=fallback, timeout_ms=5000)
+    assert rep["errors"]["total"] == 0 and rep["requests"] > 2000
+    assert min(w["requests"] for w in dead.stats()["workers"]) > 0
+    stream.close()

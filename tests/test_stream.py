@@ -145,3 +145,56 @@ def test_stream_connection_limit_and_release(hola_server):
     assert client.get("127.0.0.1", srv.port, "/api/hola").status == 200
     assert srv.stop() == 0
     s.close()
+
+
+def test_counters_of_all_workers_are_merged(hola_server, fake_aloha):
+    """The breaker's counters are kept per event-loop thread and merged when somebody looks
+    (core/breaker.h). Requests spread over eight workers must add up exactly, and failures seen by
+    different workers must trip the one circuit."""
+    srv = hola_server(args=["--aloha-url", fake_aloha.url, "--feign-max-attempts", "1"], threads=8)
+    conns = [client.Connection("127.0.0.1", srv.port) for _ in range(16)]  # two per worker (balanced placement)
+    try:
+        for c in conns:
+            for _ in range(2):
+                assert c.request("GET", "/api/hola-chaining").status == 200
+        stats = srv.stats()
+        assert [w["requests"] for w in stats["workers"]] == [4] * 8
+        time.sleep(1.1)
+        s, _ = open_stream(srv, "?delay=100")
+        events = read_events(s, 2)
+        cmd, pool = json.loads(events[0][6:]), json.loads(events[1][6:])
+        assert cmd["rollingCountSuccess"] == 32 and cmd["requestCount"] == 32 and cmd["errorCount"] == 0
+        assert pool["rollingCountThreadsExecuted"] == 32 and pool["currentCompletedTaskCount"] == 32
+        # One failure on each of six workers: no worker alone has seen five, together they have.
+        fake_aloha.mode = "500"
+        for c in conns[:12:2]:
+            assert json.loads(c.request("GET", "/api/hola-chaining").body)[1] == "Aloha response (fallback)"
+        fake_aloha.mode = "ok"
+        for c in conns[:6]:
+            c.request("GET", "/api/hola-chaining")
+        time.sleep(0.6)
+        s.close()  # events have piled up in the socket meanwhile: look through a fresh subscription
+        s, _ = open_stream(srv, "?delay=100")
+        cmd = json.loads(read_events(s, 1)[0][6:])
+        assert cmd["errorCount"] == 6 and cmd["isCircuitBreakerOpen"] is False  # 6 of 44: below 50 %
+        fake_aloha.mode = "500"
+        for _ in range(5):
+            for c in conns[:16:2]:
+                c.request("GET", "/api/hola-chaining")
+        time.sleep(0.6)
+        # The next call evaluates the closed buckets: 46 errors of 84 requests -> open, for every worker.
+        for c in conns:
+            assert json.loads(c.request("GET", "/api/hola-chaining").body) == ["Hola de unknown", "Aloha response (fallback)"]
+        n_before = len(fake_aloha.snapshot())
+        for c in conns:
+            c.request("GET", "/api/hola-chaining")
+        assert len(fake_aloha.snapshot()) == n_before  # short-circuited on all eight workers: nothing reaches aloha
+        time.sleep(1.1)
+        s.close()
+        s, _ = open_stream(srv, "?delay=100")
+        cmd = json.loads(read_events(s, 1)[0][6:])
+        assert cmd["isCircuitBreakerOpen"] is True and cmd["rollingCountShortCircuited"] >= 16
+        s.close()
+    finally:
+        for c in conns:
+            c.close()
