@@ -371,13 +371,15 @@ void Worker::on_events(uint32_t /*events*/) {
             return;
         }
         set_nodelay(fd);
+        // The connection is counted at the moment of the decision, not when the target gets round
+        // to adopting it: several acceptors deciding at the same time must see each other's choices.
         Worker* target = this;
-        if (peers_ && peers_->size() > 1) {
-            target = options_.accept_mode == AcceptMode::kRoundRobin ? (*peers_)[rr_next_++ % peers_->size()] : least_loaded();
+        if (peers_ && peers_->size() > 1 && options_.accept_mode == AcceptMode::kBalanced) {
+            target = least_loaded();  // has counted it already
+        } else {
+            if (peers_ && peers_->size() > 1) target = (*peers_)[rr_next_++ % peers_->size()];
+            target->stats_.connections_open.fetch_add(1, std::memory_order_relaxed);
         }
-        // Counted at the moment of the decision, not when the target gets round to adopting it:
-        // several acceptors deciding at the same time must see each other's choices.
-        target->stats_.connections_open.fetch_add(1, std::memory_order_relaxed);
         if (target != this) {
             target->loop().post([target, fd] { target->adopt(fd); });
         } else {
@@ -388,21 +390,25 @@ void Worker::on_events(uint32_t /*events*/) {
 
 // The worker a new connection should go to: this one if no other has fewer open connections,
 // else the least loaded (scanning from the next id on, so that ties do not all go to worker 0).
+// The connection is booked on the chosen worker with a compare-and-swap against the load that
+// made it the choice; if another acceptor got there first the scan is repeated, so two
+// simultaneous decisions can never both land on the same "emptiest" worker.
 Worker* Worker::least_loaded() {
     const std::vector<Worker*>& all = *peers_;
-    const uint64_t mine = stats_.connections_open.load(std::memory_order_relaxed);
-    Worker* best = this;
-    uint64_t best_load = mine;
     const size_t n = all.size();
-    for (size_t k = 1; k < n; ++k) {
-        Worker* w = all[(static_cast<size_t>(id_) + k) % n];
-        const uint64_t load = w->stats_.connections_open.load(std::memory_order_relaxed);
-        if (load < best_load) {
-            best = w;
-            best_load = load;
+    while (true) {
+        Worker* best = this;
+        uint64_t best_load = stats_.connections_open.load(std::memory_order_relaxed);
+        for (size_t k = 1; k < n; ++k) {
+            Worker* w = all[(static_cast<size_t>(id_) + k) % n];
+            const uint64_t load = w->stats_.connections_open.load(std::memory_order_relaxed);
+            if (load < best_load) {
+                best = w;
+                best_load = load;
+            }
         }
+        if (best->stats_.connections_open.compare_exchange_strong(best_load, best_load + 1, std::memory_order_relaxed)) return best;
     }
-    return best;
 }
 
 void Worker::adopt(int fd) {
