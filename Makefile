@@ -3,7 +3,7 @@
 # The analogue of the reference's `mvn package` producing target/hola-swarm.jar
 # (/root/reference/pom.xml:215-241): one self-contained executable, build/hola.
 #
-#   make            optimised build: build/hola build/hola-load build/libhola.so build/hola_tests
+#   make            optimised build: build/hola build/hola-load build/hola-coldstart build/hola-null build/libhola.so build/hola_tests
 #   make static     build/hola-static, fully static (for the FROM-scratch container image)
 #   make asan       AddressSanitizer + UBSan variant under build/asan/
 #   make tsan       ThreadSanitizer variant under build/tsan/
@@ -38,7 +38,7 @@ LIB_OBJ  := $(patsubst src/%.cc,$(BUILD)/obj/%.o,$(LIB_SRC))
 TEST_SRC := $(wildcard tests/cpp/*.cc)
 TEST_OBJ := $(patsubst tests/cpp/%.cc,$(BUILD)/obj/tests/%.o,$(TEST_SRC))
 
-TARGETS := $(BUILD)/hola $(BUILD)/hola-load $(BUILD)/hola-coldstart $(BUILD)/libhola.so $(BUILD)/hola_tests
+TARGETS := $(BUILD)/hola $(BUILD)/hola-load $(BUILD)/hola-coldstart $(BUILD)/hola-null $(BUILD)/libhola.so $(BUILD)/hola_tests
 
 .PHONY: all static asan tsan cov test check clean
 all: $(TARGETS)
@@ -62,6 +62,9 @@ $(BUILD)/hola-load: $(BUILD)/obj/tools/hola_load.o $(BUILD)/libhola_core.a
 	$(CXX) -o $@ $^ $(LDFLAGS)
 
 $(BUILD)/hola-coldstart: $(BUILD)/obj/tools/hola_coldstart.o $(BUILD)/libhola_core.a
+	$(CXX) -o $@ $^ $(LDFLAGS)
+
+$(BUILD)/hola-null: $(BUILD)/obj/tools/null_server.o $(BUILD)/libhola_core.a
 	$(CXX) -o $@ $^ $(LDFLAGS)
 
 $(BUILD)/libhola.so: $(BUILD)/obj/tools/capi.o $(BUILD)/libhola_core.a

@@ -40,6 +40,8 @@ std::string usage_text() {
            "  --resolve NAME=ADDRESS      answer lookups of NAME with that IPv4/IPv6 address instead of hosts file and DNS\n"
            "  --zipkin-url URL            overrides env ZIPKIN_SERVER_URL; unset/empty disables tracing\n"
            "  --zipkin-flush-ms N         span reporter period (default 1000)\n"
+           "  --zipkin-ring N             spans queued per thread before new ones are dropped (default 1024)\n"
+           "  --zipkin-max-batch N        spans per POST to the collector (default 1000, the size of the reference's queue)\n"
            "  --hystrix-config FILE       properties file with hystrix.* keys (default: the reference's config.properties values)\n"
            "  --deltaspike-properties FILE  extra config source at ordinal 100 (META-INF/apache-deltaspike.properties)\n"
            "  --webjars-dir DIR           directory served under /webjars/ (Swagger-UI assets)\n"
@@ -140,6 +142,12 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
         } else if (a == "--zipkin-flush-ms") {
             if (!value(&v) || !parse_uint(v, 3600000, &n) || n == 0) return fail("--zipkin-flush-ms needs a positive number");
             cfg->zipkin_flush_ms = static_cast<int>(n);
+        } else if (a == "--zipkin-ring") {
+            if (!value(&v) || !parse_uint(v, 1 << 22, &n) || n < 2) return fail("--zipkin-ring needs a number of spans >= 2");
+            cfg->zipkin_ring = static_cast<int>(n);
+        } else if (a == "--zipkin-max-batch") {
+            if (!value(&v) || !parse_uint(v, 1 << 22, &n) || n == 0) return fail("--zipkin-max-batch needs a positive number");
+            cfg->zipkin_max_batch = static_cast<int>(n);
         } else if (a == "--hystrix-config") {
             if (!value(&hystrix_config)) return fail("--hystrix-config needs a value");
         } else if (a == "--deltaspike-properties") {
@@ -285,7 +293,8 @@ bool Service::start(std::string* error) {
 
     greeting_.reset(new GreetingService(resolver_.get(), config_.app.hostname,
                                         [this](const std::string& m) { log("INFO", m); }));
-    tracer_.reset(new Tracer(zipkin_url, "hola", config_.zipkin_flush_ms));
+    tracer_.reset(new Tracer(zipkin_url, "hola", config_.zipkin_flush_ms, static_cast<size_t>(config_.zipkin_ring),
+                             static_cast<size_t>(config_.zipkin_max_batch)));
     if (!tracer_->error().empty()) log("WARN", tracer_->error() + " - tracing disabled");
     dns_.reset(new Resolver());
     for (const auto& kv : config_.static_hosts) dns_->set_static(kv.first, IpAddress::parse(kv.second));

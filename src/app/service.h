@@ -34,6 +34,8 @@ struct ServiceConfig {
     // Test hooks.
     std::vector<std::pair<std::string, std::string>> static_hosts;  // --resolve name=address (IPv4 or IPv6)
     int zipkin_flush_ms = 1000;
+    int zipkin_ring = 1024;        // spans queued per worker thread before new ones are dropped
+    int zipkin_max_batch = 1000;   // spans per POST (the reference's queue, and so its batch, holds 1000)
 };
 
 enum class ParseOutcome { kRun, kExitOk, kExitUsage };

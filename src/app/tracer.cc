@@ -164,13 +164,24 @@ void Tracer::thread_main() {
     }
 }
 
+// One reporting cycle: POST what has accumulated, in batches of at most max_batch_ spans, until
+// the rings are empty or the next cycle is due. The reference's collector sends one batch per
+// cycle because its queue holds no more than one batch (1000 spans); with rings that hold more
+// (--zipkin-ring) a live collector is fed as fast as it accepts.
 void Tracer::flush() {
+    const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(flush_interval_ms_);
+    while (flush_batch() == max_batch_ && !stopping_.load(std::memory_order_relaxed) && std::chrono::steady_clock::now() < deadline) {
+    }
+}
+
+size_t Tracer::flush_batch() {
     std::vector<SpanRing*> rings;
     {
         std::lock_guard<std::mutex> lock(mu_);
         for (auto& r : rings_) rings.push_back(r.get());
     }
-    std::string body = "[";
+    std::string& body = body_;
+    body.assign("[");
     size_t count = 0;
     // Take from the rings in turn so that one busy worker cannot starve the others' spans.
     bool any = true;
@@ -204,7 +215,7 @@ void Tracer::flush() {
             ++count;
         }
     }
-    if (count == 0) return;
+    if (count == 0) return 0;
     body.push_back(']');
     if (post(body)) {
         spans_reported_.fetch_add(count, std::memory_order_relaxed);
@@ -212,9 +223,11 @@ void Tracer::flush() {
     } else {
         spans_failed_.fetch_add(count, std::memory_order_relaxed);
         posts_failed_.fetch_add(1, std::memory_order_relaxed);
+        return 0;  // do not hammer a collector that is not there: wait for the next cycle
     }
-    // Anything beyond max_batch_ stays queued for the next flush; rings that are full drop at
-    // the producer, which is the reference's behaviour when its 1000-span queue is full.
+    // Rings that are full drop at the producer, which is the reference's behaviour when its
+    // 1000-span queue is full.
+    return count;
 }
 
 namespace {

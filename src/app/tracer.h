@@ -91,6 +91,7 @@ class Tracer {
  private:
     void thread_main();
     void flush();
+    size_t flush_batch();  // one POST; returns the number of spans the collector took
     bool post(const std::string& body);
 
     bool enabled_ = false;
@@ -111,6 +112,7 @@ class Tracer {
     std::vector<std::unique_ptr<SpanRing>> rings_;
     std::thread thread_;
     int sock_ = -1;  // kept open between flushes when the collector allows it
+    std::string body_;  // the batch being encoded (reporter thread only)
 
     std::atomic<uint64_t> spans_reported_{0};
     std::atomic<uint64_t> spans_failed_{0};
