@@ -70,6 +70,7 @@ class ReferenceServer:
         self.startup_seconds = 0.0
         self.threads = len(self.cpus) or None
         self._log: Optional[Path] = None
+        self.keep_log = False  # True: the log file survives stop(), so that log_tail() still works afterwards
 
     def start(self) -> "ReferenceServer":
         env = dict(os.environ)
@@ -133,7 +134,7 @@ class ReferenceServer:
                 self.proc.wait()
         code = self.proc.returncode
         self.proc = None
-        if self._log:
+        if self._log and not self.keep_log:
             try:
                 self._log.unlink()
             except OSError:

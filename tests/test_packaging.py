@@ -8,6 +8,7 @@ import os
 import re
 import socket
 import subprocess
+import time
 from pathlib import Path
 
 import hola_b200
@@ -53,6 +54,13 @@ def test_kubernetes_manifest_mirrors_the_fabric8_properties():
         assert labels[selector_key] == value  # the service actually selects the pods
 
 
+def test_licence_files():
+    """The reference is Apache-2.0 (/root/reference/LICENSE:1-201); so is the rebuild."""
+    text = (REPO / "LICENSE").read_text()
+    assert "Apache License" in text and "Version 2.0, January 2004" in text and "END OF TERMS AND CONDITIONS" in text
+    assert "Apache License, Version 2.0" in (REPO / "NOTICE").read_text()
+
+
 def test_sample_config_files_are_loadable(hola_server):
     from hola_b200 import client, native
     entries = dict(native.properties_parse((REPO / "translation.properties").read_bytes()))
@@ -80,3 +88,77 @@ def test_cold_start_is_measured_in_milliseconds():
                              port=port, runs=5, env=env)
     assert len(rep["runs"]) == 5 and rep["unit"] == "us"
     assert 100 < rep["median"] < 500_000  # the JVM service is given 5 s before its first probe (pom.xml:93)
+
+
+def _can_chroot() -> bool:
+    if os.geteuid() != 0:
+        return False
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        return subprocess.run(["python3", "-c", "import os,sys; os.chroot(sys.argv[1])", d], capture_output=True).returncode == 0
+
+
+import pytest  # noqa: E402
+
+
+@pytest.mark.slow
+@pytest.mark.skipif(not _can_chroot(), reason="needs root and CAP_SYS_CHROOT")
+def test_static_executable_in_an_empty_root_filesystem(tmp_path, fake_aloha):
+    """BASELINE.json config 5 is "the same 64-client load inside the container image"; no box this
+    project sees has a container runtime, so the image (Dockerfile: FROM scratch + /app/hola) was
+    never built. The closest thing that can run is what that image *is*: the static executable
+    alone in an empty root directory - no /etc, no /proc, no /sys, no libraries, no resolv.conf -
+    entered with chroot(2). Not a container (no namespaces, no cgroup limits), and labelled so in
+    BASELINE.md; but it proves the executable needs nothing the scratch image does not have.
+    (/root/reference/Dockerfile:1-10 ships a JVM base image instead; /root/reference/pom.xml:247-280.)"""
+    from hola_b200 import client
+    static = hola_b200.build("static").hola
+    root = tmp_path / "rootfs"
+    (root / "app").mkdir(parents=True)
+    target = root / "app" / "hola"
+    target.write_bytes(static.read_bytes())
+    target.chmod(0o755)
+    assert sorted(p.name for p in root.rglob("*")) == ["app", "hola"]
+
+    def launch(*args):
+        port = free_port()
+        env = {"ZIPKIN_SERVER_URL": "http://zipkin-query:9411"}  # as the image sets it (Dockerfile:6); HOSTNAME stays unset
+        proc = subprocess.Popen(["/app/hola", "--port", str(port), "--bind", "127.0.0.1", "--threads", "2", *args], env=env,
+                                stdout=subprocess.PIPE, stderr=subprocess.PIPE, preexec_fn=lambda: (os.chroot(str(root)), os.chdir("/")))
+        deadline = time.time() + 5
+        while time.time() < deadline:
+            try:
+                if client.get("127.0.0.1", port, "/api/health", timeout=1).status == 200:
+                    return proc, port
+            except OSError:
+                time.sleep(0.02)
+        proc.kill()
+        raise AssertionError("did not start in the empty root: " + proc.stderr.read().decode()[-500:])
+
+    # 1. As the image starts it: greeting, fallback with no resolver configuration whatsoever.
+    proc, port = launch()
+    try:
+        r = client.get("127.0.0.1", port, "/api/hola")
+        assert (r.status, r.body) == (200, b"Hola de unknown") and r.header("Access-Control-Allow-Origin") == "*"
+        t0 = time.time()
+        r = client.get("127.0.0.1", port, "/api/hola-chaining")  # `aloha` cannot resolve: no resolv.conf, no hosts file
+        assert json.loads(r.body) == ["Hola de unknown", "Aloha response (fallback)"] and time.time() - t0 < 2.0
+        assert client.get("127.0.0.1", port, "/").status == 200
+        # 2. The 64-client load of config 4/5, shortened to 10 s.
+        rep = loadgen.run("http://127.0.0.1:%d/api/hola" % port, connections=64, duration=10, warmup=1, threads=2,
+                          expect_body=b"Hola de unknown")
+        assert rep["errors"]["total"] == 0 and rep["requests"] > 10_000
+        print("\nconfig-5 proxy (chroot, static, 2 server threads, unpinned): %.0f req/s p50 %.1f us p99 %.1f us" %
+              (rep["rps"], rep["latency_us"]["p50"], rep["latency_us"]["p99"]))
+    finally:
+        proc.terminate()
+        assert proc.wait(10) == 0
+    # 3. The downstream name pinned with --resolve: the success path, still with nothing in the root.
+    proc, port = launch("--resolve", "aloha=127.0.0.1", "--aloha-url", "http://aloha:%d/" % fake_aloha.port)
+    try:
+        r = client.get("127.0.0.1", port, "/api/hola-chaining")
+        assert json.loads(r.body) == ["Hola de unknown"] + fake_aloha.payload
+        assert fake_aloha.snapshot()[0]["headers"]["host"] == "aloha:%d" % fake_aloha.port
+    finally:
+        proc.terminate()
+        assert proc.wait(10) == 0

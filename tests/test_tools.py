@@ -178,6 +178,36 @@ def test_differential_tool_same_and_different(hola_server):
     assert any("/api/hola" in r for r in changed) and not any("/api/health" in r for r in changed)
 
 
+@pytest.mark.slow
+def test_differential_tool_reports_every_unverified_decision(native_build):
+    """DESIGN.md section 4 lists what was decided from memory of libraries that cannot be run here.
+    The differential tool turns that list into a machine-readable report: when it starts both
+    services itself (so that it owns their span collectors, their logs and their greeting pattern)
+    every item is compared; here both sides are this service, so every compared item is `same`."""
+    tool = str(REPO / "tools" / "differential.py")
+    hola = "%s --port {port} --bind 127.0.0.1 --zipkin-flush-ms 50 --aloha-url http://127.0.0.1:9/ --feign-max-attempts 1" % native_build.hola
+    out = subprocess.run([sys.executable, tool, "--launch-left", hola + " --threads 1 --reference-logging",
+                          "--launch-right", hola + " --threads 2 --accept-mode rr --log-feign", "--json"],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    rep = json.loads(out.stdout)
+    items = {i["id"]: i for i in rep["items"]}
+    compared = {"response-head", "error-bodies", "chaining-json-whitespace", "swagger-text", "hystrix-stream-fields", "zipkin-span-json",
+                "b3-ids-need-sampled-header", "feign-basic-log", "formatter-corner-cases"}
+    assert compared <= set(items)
+    assert {i for i in compared if items[i]["status"] != "same"} == set(), {i: items[i] for i in compared if items[i]["status"] != "same"}
+    assert items["feign-basic-log"]["details"]["left"]  # the lines were really there to compare
+    assert items["dns-cache-ttl"]["status"] == "not-compared" and items["feign-retryer-schedule"]["status"] == "not-compared"
+    # Against something else the same items come back `different` (or not comparable), not as a crash.
+    standin = "%s %s {port}" % (sys.executable, REPO / "tests" / "data" / "standin_reference.py")
+    out = subprocess.run([sys.executable, tool, "--launch-left", hola + " --threads 1", "--launch-right", standin, "--json"],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 1
+    items = {i["id"]: i for i in json.loads(out.stdout)["items"]}
+    assert items["response-head"]["status"] == "different" and items["swagger-text"]["status"] == "different"
+    assert items["formatter-corner-cases"]["status"] == "not-compared"
+
+
 def test_graft_entry_build_and_smoke():
     sys.path.insert(0, str(REPO))
     import __graft_entry__
