@@ -91,9 +91,11 @@ def mode_settings(mode: str):
     return env, args, expect
 
 
-def make_server(impl: str, mode: str, server_cpus: Sequence[int], threads: int):
+def make_server(impl: str, mode: str, server_cpus: Sequence[int], threads: int, io_backend: str = "epoll"):
     """The process under test: this repository's executable, or the reference (hola_b200/reference.py)."""
     env, args, _ = mode_settings(mode)
+    if io_backend != "epoll":
+        args = args + ["--io-backend", io_backend]
     if impl == "reference":
         from hola_b200.reference import ReferenceServer, reference_command
         command, _why = reference_command()
@@ -135,7 +137,7 @@ def coldstart_ms(impl: str, mode: str, runs: int = 5) -> Optional[Dict]:
 
 
 def run_instance(index: int, cpus: Sequence[int], steps: int, warmup: int, mode: str, impl: str, results: Dict[int, Dict],
-                 half_load_seconds: int = 0) -> None:
+                 half_load_seconds: int = 0, io_backend: str = "epoll") -> None:
     from hola_b200 import loadgen
 
     cpus = list(cpus)
@@ -147,7 +149,7 @@ def run_instance(index: int, cpus: Sequence[int], steps: int, warmup: int, mode:
     server_threads = min(len(server_cpus), CONNECTIONS)
     load_threads = min(len(load_cpus), CONNECTIONS)
     _, _, expect = mode_settings(mode)
-    with make_server(impl, mode, server_cpus, server_threads) as srv:
+    with make_server(impl, mode, server_cpus, server_threads, io_backend) as srv:
         before = srv.stats()
         report = loadgen.run(srv.base_url + "/api/hola", connections=CONNECTIONS, duration=steps, warmup=warmup,
                              interval=1.0, threads=load_threads, cpus=load_cpus, expect_body=expect)
@@ -166,6 +168,7 @@ def run_instance(index: int, cpus: Sequence[int], steps: int, warmup: int, mode:
                 "user": round((after["cpu_user_s"] - before["cpu_user_s"]) * 1e6 / total, 3),
                 "sys": round((after["cpu_sys_s"] - before["cpu_sys_s"]) * 1e6 / total, 3)}
             report["accept_mode"] = after["accept_mode"]
+            report["io_backend"] = after.get("io_backend")
         if half_load_seconds > 0:
             # Context for the headline, outside its timed region: the same 64 connections driven
             # open-loop at half the measured throughput, latency taken from the scheduled send time.
@@ -196,6 +199,8 @@ def main() -> int:
                     help="after the timed run (N=1 only): an open-loop run at half the measured rate for this many "
                          "seconds, reported as `half_load` (0 to skip)")
     ap.add_argument("--coldstart-runs", type=int, default=5, help="launches for `coldstart_ms` (0 to skip)")
+    ap.add_argument("--io-backend", choices=["epoll", "uring"], default=os.environ.get("HOLA_BENCH_IO_BACKEND", "epoll"),
+                    help="the service's --io-backend (ours only)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3  # timing rule: W >= 3
@@ -250,7 +255,7 @@ def main() -> int:
     def guarded(i: int) -> None:
         try:
             run_instance(i, slices[i % len(slices)], args.steps, args.warmup, args.mode, args.impl, results,
-                         half_load_seconds=args.half_load_seconds if (n == 1 and not distributed) else 0)
+                         half_load_seconds=args.half_load_seconds if (n == 1 and not distributed) else 0, io_backend=args.io_backend)
         except Exception as exc:  # noqa: BLE001 - reported below, on every rank
             results[i] = {"error": "%s: %s" % (type(exc).__name__, exc)}
 
@@ -350,6 +355,7 @@ def main() -> int:
             "connections_per_instance": CONNECTIONS,
             "mode": args.mode,
             "accept_mode": first.get("accept_mode"),
+            "io_backend": first.get("io_backend"),
             "housekeeping_cpu": housekeeping,
             "server_cpus": first["server_cpus"],
             "load_cpus": first["load_cpus"],

@@ -34,6 +34,9 @@ std::string usage_text() {
            "  --accept-mode MODE          balanced (default: a listener per thread, new connections go to the least-loaded\n"
            "                              thread) | reuseport (a listener per thread, the kernel's hash decides) |\n"
            "                              rr (one acceptor deals connections in turn; no SO_REUSEPORT)\n"
+           "  --io-backend BACKEND        epoll (default: readiness, one recv and one send per request) | uring (io_uring:\n"
+           "                              multishot receives into kernel-picked buffers, sends batched into one system call\n"
+           "                              per loop iteration; falls back to epoll where the kernel refuses it)\n"
            "  --aloha-url URL             downstream base URL (default http://aloha:8080/)\n"
            "  --feign-max-attempts N      tries per downstream call on connection failures (default 5, as Feign's\n"
            "                              default Retryer: pauses of 150, 225, 337, 506 ms; 1 disables retrying)\n"
@@ -119,6 +122,9 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
         } else if (a == "--accept-mode") {
             if (!value(&v) || (v != "balanced" && v != "reuseport" && v != "rr")) return fail("--accept-mode is balanced, reuseport or rr");
             cfg->server.accept_mode = v == "balanced" ? AcceptMode::kBalanced : v == "reuseport" ? AcceptMode::kReusePort : AcceptMode::kRoundRobin;
+        } else if (a == "--io-backend") {
+            if (!value(&v) || (v != "epoll" && v != "uring")) return fail("--io-backend is epoll or uring");
+            cfg->server.io_backend = v == "uring" ? IoBackend::kUring : IoBackend::kEpoll;
         } else if (a == "--aloha-url") {
             std::string host, path;
             uint16_t port = 80;
@@ -326,12 +332,13 @@ std::string Service::stats_json() const {
     char buf[512];
     std::snprintf(buf, sizeof buf,
                   "{\"requests\":%llu,\"bad_requests\":%llu,\"connections_accepted\":%llu,\"connections_open\":%llu,"
-                  "\"cpu_user_s\":%.6f,\"cpu_sys_s\":%.6f,\"accept_mode\":\"%s\",\"threads\":%d,"
+                  "\"cpu_user_s\":%.6f,\"cpu_sys_s\":%.6f,\"accept_mode\":\"%s\",\"io_backend\":\"%s\",\"threads\":%d,"
                   "\"spans\":{\"reported\":%llu,\"dropped\":%llu,\"posts_ok\":%llu,\"posts_failed\":%llu},\"workers\":[",
                   static_cast<unsigned long long>(st.requests), static_cast<unsigned long long>(st.bad_requests),
                   static_cast<unsigned long long>(st.connections_accepted), static_cast<unsigned long long>(st.connections_open),
                   static_cast<double>(ru.ru_utime.tv_sec) + static_cast<double>(ru.ru_utime.tv_usec) / 1e6,
-                  static_cast<double>(ru.ru_stime.tv_sec) + static_cast<double>(ru.ru_stime.tv_usec) / 1e6, mode, server_->threads(),
+                  static_cast<double>(ru.ru_stime.tv_sec) + static_cast<double>(ru.ru_stime.tv_usec) / 1e6, mode, server_->io_backend_name(),
+                  server_->threads(),
                   static_cast<unsigned long long>(ts.spans_reported), static_cast<unsigned long long>(ts.spans_dropped),
                   static_cast<unsigned long long>(ts.posts_ok), static_cast<unsigned long long>(ts.posts_failed));
     std::string out = buf;

@@ -1,14 +1,22 @@
 #include "net/event_loop.h"
 
+#include <poll.h>
 #include <sys/eventfd.h>
 #include <unistd.h>
 
 #include <cerrno>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <ctime>
 
+#include "net/uring.h"
+
 namespace hola {
+
+namespace {
+constexpr uint64_t kEpollPollTag = 1;  // user_data of the multishot poll on the epoll descriptor (handler slots start at 1 << 32)
+}
 
 int64_t monotonic_ns() {
     timespec ts;
@@ -38,6 +46,7 @@ EventLoop::EventLoop() {
 
 EventLoop::~EventLoop() {
     for (auto& fn : deferred_) fn();  // pending deletions
+    uring_.reset();                   // cancels whatever is still in flight on the ring
     if (wake_fd_ >= 0) close(wake_fd_);
     if (epfd_ >= 0) close(epfd_);
 }
@@ -126,7 +135,117 @@ int EventLoop::next_timeout_ms() const {
     return ms > 1000 ? 1000 : static_cast<int>(ms);
 }
 
+void EventLoop::dispatch_epoll(int n, epoll_event* events) {
+    bool woken = false;
+    for (int i = 0; i < n; ++i) {
+        auto* handler = static_cast<EventHandler*>(events[i].data.ptr);
+        if (!handler) {
+            woken = true;
+            continue;
+        }
+        handler->on_events(events[i].events);
+    }
+    if (woken) drain_mailbox();
+}
+
+// ---- completion-based mode --------------------------------------------------------------------
+
+bool EventLoop::enable_uring(unsigned entries, unsigned buffers, unsigned buffer_size) {
+    std::unique_ptr<Uring> ring(new Uring());
+    int rc = ring->init(entries);
+    if (rc == 0) rc = ring->setup_buffers(1, buffers, buffer_size);
+    if (rc != 0) {
+        std::fprintf(stderr, "hola: io_uring is not usable here (%s) - staying with epoll\n", std::strerror(-rc));
+        return false;
+    }
+    uring_ = std::move(ring);
+    return true;
+}
+
+int EventLoop::register_uring_handler(UringHandler* h) {
+    uring_handlers_.push_back(h);
+    return static_cast<int>(uring_handlers_.size()) - 1;
+}
+
+io_uring_sqe* EventLoop::uring_sqe() {
+    io_uring_sqe* sqe = uring_->get_sqe();
+    if (!sqe) {
+        uring_->submit_and_wait_for(0);  // queue full: hand what is there to the kernel
+        sqe = uring_->get_sqe();
+        if (!sqe) {
+            std::fprintf(stderr, "hola: io_uring submission queue stays full\n");
+            std::abort();
+        }
+    }
+    return sqe;
+}
+
+uint16_t EventLoop::uring_buffer_group() const { return uring_->buffer_group(); }
+
+void EventLoop::arm_epoll_poll() {
+    io_uring_sqe* sqe = uring_sqe();
+    sqe->opcode = IORING_OP_POLL_ADD;
+    sqe->fd = epfd_;
+    sqe->poll32_events = POLLIN;
+    sqe->len = IORING_POLL_ADD_MULTI;
+    sqe->user_data = kEpollPollTag;
+}
+
+// One iteration = one io_uring_enter: it submits everything the handlers queued during the
+// previous iteration (sends, re-armed receives) and waits for the next completions, bounded by
+// the next timer. The epoll set rides along as one multishot poll on the epoll descriptor.
+void EventLoop::run_uring() {
+    constexpr int kMaxEvents = 256;
+    epoll_event events[kMaxEvents];
+    arm_epoll_poll();
+    while (!stop_.load(std::memory_order_acquire)) {
+        const int timeout_ms = next_timeout_ms();
+        if (timeout_ms != 0) ++stats_.blocking_waits;
+        const int rc = uring_->submit_and_wait_for(static_cast<int64_t>(timeout_ms) * 1000000);
+        refresh_clock();
+        ++stats_.iterations;
+        if (rc != 0 && rc != -ETIME && rc != -EINTR && rc != -EAGAIN && rc != -EBUSY) {
+            std::fprintf(stderr, "hola: io_uring_enter: %s\n", std::strerror(-rc));
+            break;
+        }
+        bool epoll_ready = false;
+        for (const io_uring_cqe* cqe = uring_->peek(); cqe; cqe = uring_->peek()) {
+            const uint64_t user_data = cqe->user_data;
+            const int32_t res = cqe->res;
+            const uint32_t flags = cqe->flags;
+            uring_->seen();
+            ++stats_.events;
+            if (user_data == kEpollPollTag) {
+                epoll_ready = true;
+                if (!(flags & IORING_CQE_F_MORE)) arm_epoll_poll();
+                continue;
+            }
+            const size_t slot = static_cast<size_t>(user_data >> 32) - 1;
+            const char* data = nullptr;
+            uint16_t bid = 0;
+            if (flags & IORING_CQE_F_BUFFER) {
+                bid = static_cast<uint16_t>(flags >> IORING_CQE_BUFFER_SHIFT);
+                data = uring_->buffer(bid);
+            }
+            if (slot < uring_handlers_.size()) uring_handlers_[slot]->on_completion(static_cast<uint32_t>(user_data), res, flags, data);
+            if (flags & IORING_CQE_F_BUFFER) uring_->recycle_buffer(bid, true);
+        }
+        last_event_ns_ = now_ns_;
+        if (epoll_ready) {
+            const int n = epoll_wait(epfd_, events, kMaxEvents, 0);
+            if (n > 0) dispatch_epoll(n, events);
+        }
+        run_timers();
+        run_deferred();
+    }
+    run_deferred();
+}
+
 void EventLoop::run() {
+    if (uring_) {
+        run_uring();
+        return;
+    }
     constexpr int kMaxEvents = 256;
     epoll_event events[kMaxEvents];
     while (!stop_.load(std::memory_order_acquire)) {
@@ -162,16 +281,7 @@ void EventLoop::run() {
             std::perror("hola: epoll_wait");
             break;
         }
-        bool woken = false;
-        for (int i = 0; i < n; ++i) {
-            auto* handler = static_cast<EventHandler*>(events[i].data.ptr);
-            if (!handler) {
-                woken = true;
-                continue;
-            }
-            handler->on_events(events[i].events);
-        }
-        if (woken) drain_mailbox();
+        dispatch_epoll(n, events);
         run_timers();
         run_deferred();
     }

@@ -1,4 +1,5 @@
-// One epoll instance + timer heap + cross-thread mailbox, driven by exactly one thread.
+// One epoll instance + timer heap + cross-thread mailbox, driven by exactly one thread; optionally
+// with an io_uring instance in front of it for completion-based socket I/O.
 //
 // The reference borrows its I/O model from Undertow/XNIO (I/O threads + a worker pool,
 // /root/reference/pom.xml:122-129). The rebuild uses one event loop per core instead: a
@@ -12,10 +13,13 @@
 #include <atomic>
 #include <cstdint>
 #include <functional>
+#include <memory>
 #include <mutex>
 #include <queue>
 #include <unordered_map>
 #include <vector>
+
+struct io_uring_sqe;  // <linux/io_uring.h>
 
 namespace hola {
 
@@ -25,6 +29,17 @@ class EventHandler {
     virtual void on_events(uint32_t events) = 0;
 };
 
+// Receiver of io_uring completions (uring mode only). `tag` is whatever the submitter put into
+// the low 32 bits of the request's user_data; `data` points at the received bytes for a receive
+// that used a provided buffer (valid during the call only), else it is null.
+class UringHandler {
+ public:
+    virtual ~UringHandler() = default;
+    virtual void on_completion(uint32_t tag, int32_t res, uint32_t cqe_flags, const char* data) = 0;
+};
+
+class Uring;
+
 int64_t monotonic_ns();
 int64_t realtime_us();
 
@@ -33,7 +48,7 @@ class EventLoop {
     using TimerId = uint64_t;
 
     EventLoop();
-    ~EventLoop();
+    ~EventLoop();  // out of line: Uring is an incomplete type here
     EventLoop(const EventLoop&) = delete;
     EventLoop& operator=(const EventLoop&) = delete;
 
@@ -73,6 +88,20 @@ class EventLoop {
     void stop();  // safe from any thread
     bool stopping() const { return stop_.load(std::memory_order_relaxed); }
 
+    // Completion-based I/O. enable_uring() must be called on the loop's own thread before run();
+    // it returns false (and the loop stays a plain epoll loop) when the kernel refuses. In uring
+    // mode the epoll set is still served - it is polled through the ring - so listeners, the
+    // mailbox and the outbound client work unchanged; sockets that want completions register a
+    // UringHandler and submit their own receives and sends:
+    //     sqe = loop.uring_sqe(); fill it; sqe->user_data = loop.uring_user_data(slot, tag);
+    // Submissions are flushed once per loop iteration, together with the wait for completions.
+    bool enable_uring(unsigned entries = 4096, unsigned buffers = 1024, unsigned buffer_size = 4096);
+    bool uring_enabled() const { return uring_ != nullptr; }
+    int register_uring_handler(UringHandler* h);
+    static uint64_t uring_user_data(int slot, uint32_t tag) { return (static_cast<uint64_t>(slot + 1) << 32) | tag; }
+    ::io_uring_sqe* uring_sqe();  // never null: flushes the submission queue when it is full
+    uint16_t uring_buffer_group() const;
+
     // Deferred deletion: objects whose handlers may still be referenced by the current batch of
     // epoll events are parked here and destroyed at the end of the iteration.
     void defer(std::function<void()> fn) { deferred_.push_back(std::move(fn)); }
@@ -87,6 +116,9 @@ class EventLoop {
     void drain_mailbox();
     void run_timers();
     void run_deferred();
+    void run_uring();
+    void dispatch_epoll(int n, epoll_event* events);
+    void arm_epoll_poll();
     int next_timeout_ms() const;
 
     int epfd_ = -1;
@@ -104,6 +136,8 @@ class EventLoop {
     std::vector<std::function<void()>> mailbox_;
     std::atomic<bool> mailbox_signalled_{false};
     std::vector<std::function<void()>> deferred_;
+    std::unique_ptr<Uring> uring_;
+    std::vector<UringHandler*> uring_handlers_;
     int64_t spin_ns_ = 0;
     int64_t last_event_ns_ = 0;
     LoopStats stats_;

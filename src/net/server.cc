@@ -2,6 +2,7 @@
 
 #include <arpa/inet.h>
 #include <fcntl.h>
+#include <linux/io_uring.h>
 #include <netinet/in.h>
 #include <netinet/tcp.h>
 #include <pthread.h>
@@ -49,6 +50,7 @@ void set_nodelay(int fd) {
 
 Connection::~Connection() {
     if (fd_ >= 0) close(fd_);
+    if (zombie_fd_ >= 0) close(zombie_fd_);
 }
 
 void Connection::start(int fd) {
@@ -64,6 +66,16 @@ void Connection::start(int fd) {
     discard_remaining_ = 0;
     discard_chunked_.reset();
     last_active_ns_ = worker_->loop().now_ns();
+    if (worker_->loop().uring_enabled()) {
+        uring_ = true;
+        if (uring_slot_ < 0) uring_slot_ = worker_->loop().register_uring_handler(this);
+        recv_armed_ = recv_cancelling_ = send_inflight_ = zombie_ = false;
+        ops_ = 0;
+        sending_.clear();
+        sending_sent_ = 0;
+        uring_arm_recv();
+        return;
+    }
     registered_events_ = EPOLLIN | EPOLLRDHUP;
     if (!worker_->loop().add(fd_, registered_events_, this)) close_now();
 }
@@ -72,8 +84,18 @@ void Connection::close_now() {
     if (fd_ < 0) return;
     const ConnRef old = ref();
     const bool notify = deferred_ || streaming_;
-    worker_->loop().remove(fd_);
-    close(fd_);
+    if (uring_) {
+        // Operations in flight hold the socket open and will still complete. shutdown() makes
+        // them complete now; the descriptor is closed, and the slot given back, by the last one.
+        zombie_fd_ = fd_;
+        if (ops_ > 0) {
+            zombie_ = true;
+            shutdown(fd_, SHUT_RDWR);
+        }
+    } else {
+        worker_->loop().remove(fd_);
+        close(fd_);
+    }
     fd_ = -1;
     ++generation_;
     deferred_ = streaming_ = false;
@@ -84,8 +106,154 @@ void Connection::close_now() {
     if (out_.capacity() > 65536) std::string().swap(out_);
     out_.clear();
     if (notify) worker_->app_->on_connection_closed(*worker_, old);
+    if (zombie_) return;  // uring_reap_zombie() finishes the job
+    if (zombie_fd_ >= 0) {
+        close(zombie_fd_);
+        zombie_fd_ = -1;
+    }
     worker_->release(this);
 }
+
+// ---- io_uring backend ---------------------------------------------------------------------------
+
+namespace {
+enum : uint32_t { kOpRecv = 1, kOpSend = 2, kOpCancel = 3 };
+}
+
+void Connection::uring_reap_zombie() {
+    if (!zombie_ || ops_ > 0) return;
+    zombie_ = false;
+    close(zombie_fd_);
+    zombie_fd_ = -1;
+    if (sending_.capacity() > 65536) std::string().swap(sending_);
+    sending_.clear();
+    sending_sent_ = 0;
+    worker_->release(this);
+}
+
+void Connection::uring_arm_recv() {
+    EventLoop& loop = worker_->loop();
+    io_uring_sqe* sqe = loop.uring_sqe();
+    sqe->opcode = IORING_OP_RECV;
+    sqe->fd = fd_;
+    sqe->ioprio = IORING_RECV_MULTISHOT;
+    sqe->flags = IOSQE_BUFFER_SELECT;
+    sqe->buf_group = loop.uring_buffer_group();
+    sqe->user_data = EventLoop::uring_user_data(uring_slot_, kOpRecv);
+    recv_armed_ = true;
+    recv_cancelling_ = false;
+    ++ops_;
+}
+
+void Connection::uring_cancel_recv() {
+    io_uring_sqe* sqe = worker_->loop().uring_sqe();
+    sqe->opcode = IORING_OP_ASYNC_CANCEL;
+    sqe->addr = EventLoop::uring_user_data(uring_slot_, kOpRecv);
+    sqe->user_data = EventLoop::uring_user_data(uring_slot_, kOpCancel);
+    recv_cancelling_ = true;
+    ++ops_;
+}
+
+void Connection::uring_submit_send() {
+    io_uring_sqe* sqe = worker_->loop().uring_sqe();
+    sqe->opcode = IORING_OP_SEND;
+    sqe->fd = fd_;
+    sqe->addr = reinterpret_cast<uint64_t>(sending_.data() + sending_sent_);
+    sqe->len = static_cast<uint32_t>(std::min<size_t>(sending_.size() - sending_sent_, 1u << 30));
+    sqe->msg_flags = MSG_NOSIGNAL;
+    sqe->user_data = EventLoop::uring_user_data(uring_slot_, kOpSend);
+    send_inflight_ = true;
+    ++ops_;
+}
+
+void Connection::uring_input(const char* data, size_t len) {
+    if (streaming_) return;  // a metrics stream has no use for further input
+    if (in_pos_ > 0 && in_pos_ == in_len_) in_pos_ = in_len_ = 0;
+    if (in_len_ + len > in_cap_) {
+        if (in_pos_ > 0) {
+            std::memmove(in_.get(), in_.get() + in_pos_, in_len_ - in_pos_);
+            in_len_ -= in_pos_;
+            in_pos_ = 0;
+        }
+        if (in_len_ + len > in_cap_) {
+            // Unlike a readiness loop, completions cannot be refused: the bytes are here. Input
+            // is throttled by cancelling the receive (update_interest), which leaves at most what
+            // the socket had buffered; a peer that still gets far beyond the limit is dropped.
+            const size_t hard_limit = 4 * (worker_->options().max_header_bytes + kInitialInputCapacity) + (1u << 20);
+            if (in_len_ + len > hard_limit) {
+                close_now();
+                return;
+            }
+            size_t new_cap = in_cap_ ? in_cap_ : kInitialInputCapacity;
+            while (new_cap < in_len_ + len) new_cap *= 2;
+            std::unique_ptr<char[]> bigger(new char[new_cap]);
+            std::memcpy(bigger.get(), in_.get(), in_len_);
+            in_ = std::move(bigger);
+            in_cap_ = new_cap;
+        }
+    }
+    std::memcpy(in_.get() + in_len_, data, len);
+    in_len_ += len;
+    last_active_ns_ = worker_->loop().now_ns();
+    process_input();
+}
+
+void Connection::on_completion(uint32_t tag, int32_t res, uint32_t cqe_flags, const char* data) {
+    switch (tag & 3u) {
+        case kOpRecv: {
+            const bool more = (cqe_flags & IORING_CQE_F_MORE) != 0;
+            if (!more) {
+                recv_armed_ = recv_cancelling_ = false;
+                --ops_;
+            }
+            if (zombie_ || fd_ < 0) {
+                uring_reap_zombie();
+                return;
+            }
+            if (res > 0) {
+                if (data) uring_input(data, static_cast<size_t>(res));
+            } else if (res == 0) {
+                peer_closed_ = true;
+                if (streaming_ || (!deferred_ && !output_pending())) {
+                    close_now();
+                    return;
+                }
+                close_after_write_ = true;  // finish what is owed, then close
+            } else if (res != -ENOBUFS && res != -ECANCELED && res != -EINTR && res != -EAGAIN) {
+                close_now();
+                return;
+            }
+            if (fd_ >= 0 && !more) update_interest();  // a multishot that ended is re-armed when reading is still wanted
+            return;
+        }
+        case kOpSend:
+            --ops_;
+            send_inflight_ = false;
+            if (zombie_ || fd_ < 0) {
+                uring_reap_zombie();
+                return;
+            }
+            if (res < 0 && res != -EINTR && res != -EAGAIN) {
+                close_now();
+                return;
+            }
+            if (res > 0) {
+                sending_sent_ += static_cast<size_t>(res);
+                if (sending_sent_ < sending_.size()) want_write_ = true;  // short send: the peer is not keeping up
+            }
+            flush();
+            return;
+        case kOpCancel:
+            --ops_;
+            uring_reap_zombie();
+            return;
+        default:
+            return;
+    }
+}
+
+// ---- both backends --------------------------------------------------------------------------------
+
 
 bool Connection::input_full() const {
     return in_pos_ == 0 && in_len_ == in_cap_ && in_cap_ >= worker_->options().max_header_bytes + kInitialInputCapacity;
@@ -93,6 +261,18 @@ bool Connection::input_full() const {
 
 void Connection::update_interest() {
     if (fd_ < 0) return;
+    if (uring_) {
+        // The same decisions as below, expressed as "is a receive in flight".
+        bool can_read = !want_write_ || streaming_;
+        if (deferred_ && in_len_ - in_pos_ >= worker_->options().max_header_bytes) can_read = false;
+        if (peer_closed_) can_read = false;
+        if (can_read && !recv_armed_) {
+            uring_arm_recv();
+        } else if (!can_read && recv_armed_ && !recv_cancelling_) {
+            uring_cancel_recv();
+        }
+        return;
+    }
     uint32_t ev = EPOLLRDHUP;
     if (want_write_) ev |= EPOLLOUT;
     bool can_read = !want_write_ || streaming_;
@@ -260,6 +440,27 @@ void Connection::process_input() {
 
 void Connection::flush() {
     if (fd_ < 0) return;
+    if (uring_) {
+        if (send_inflight_) return;  // its completion comes back here
+        if (sending_sent_ >= sending_.size()) {
+            sending_.clear();
+            sending_sent_ = 0;
+            if (!out_.empty()) out_.swap(sending_);  // out_ gets the other buffer, with its capacity
+        }
+        if (sending_sent_ < sending_.size()) {
+            if (sending_.size() - sending_sent_ > (1u << 20)) want_write_ = true;
+            uring_submit_send();
+            if (want_write_) update_interest();
+            return;
+        }
+        want_write_ = false;
+        if (close_after_write_ && !deferred_ && !streaming_) {
+            close_now();
+            return;
+        }
+        update_interest();
+        return;
+    }
     while (out_sent_ < out_.size()) {
         const ssize_t n = send(fd_, out_.data() + out_sent_, out_.size() - out_sent_, MSG_NOSIGNAL);
         if (n > 0) {
@@ -412,11 +613,6 @@ Worker* Worker::least_loaded() {
 }
 
 void Worker::adopt(int fd) {
-    if (draining_) {
-        close(fd);
-        stats_.connections_open.fetch_sub(1, std::memory_order_relaxed);
-        return;
-    }
     Connection* c;
     if (!free_.empty()) {
         c = conns_[free_.back()].get();
@@ -428,6 +624,23 @@ void Worker::adopt(int fd) {
     ++open_count_;
     stats_.connections_accepted.fetch_add(1, std::memory_order_relaxed);
     c->start(fd);
+    if (draining_ && c->fd_ >= 0) {
+        // Handed over by a peer that accepted it just before the shutdown began. The client has
+        // a connection and may already have written its request: closing now would turn a clean
+        // shutdown into a failed request. It gets the same deal as every other connection - its
+        // request is answered (with "Connection: close", since draining() is true) - and is
+        // closed after the linger period if it stays silent.
+        const ConnRef ref = c->ref();
+        loop_.add_timer(loop_.now_ns() + static_cast<int64_t>(std::max(1, options_.drain_linger_ms)) * 1000000, [this, ref] {
+            Connection* late = lookup(ref);
+            if (!late) return;
+            if (!late->deferred_ && !late->output_pending()) {
+                late->close_now();
+            } else {
+                late->close_after_write_ = true;
+            }
+        });
+    }
 }
 
 void Worker::release(Connection* c) {
@@ -468,7 +681,7 @@ bool Worker::complete(ConnRef ref, std::string_view response, bool close_after) 
 bool Worker::stream_write(ConnRef ref, std::string_view bytes) {
     Connection* c = lookup(ref);
     if (!c || !c->streaming_) return false;
-    if (c->out_.size() - c->out_sent_ > (4u << 20)) {  // reader is not keeping up
+    if (c->out_.size() - c->out_sent_ + c->sending_.size() - c->sending_sent_ > (4u << 20)) {  // reader is not keeping up
         c->close_now();
         return false;
     }
@@ -482,7 +695,7 @@ void Worker::sweep_idle() {
     const int64_t now = loop_.now_ns();
     for (auto& c : conns_) {
         if (c->fd_ < 0 || c->deferred_ || c->streaming_) continue;
-        if (c->out_sent_ < c->out_.size()) continue;
+        if (c->output_pending()) continue;
         if (now - c->last_active_ns_ > limit) c->close_now();
     }
     if (!draining_) {
@@ -514,7 +727,7 @@ void Worker::begin_drain() {
     auto close_idle = [this] {
         for (auto& c : conns_) {
             if (c->fd_ < 0) continue;
-            if (!c->deferred_ && c->out_sent_ >= c->out_.size()) {
+            if (!c->deferred_ && !c->output_pending()) {
                 c->close_now();
             } else {
                 c->close_after_write_ = true;
@@ -543,6 +756,7 @@ void Worker::thread_main() {
     std::snprintf(name, sizeof name, "hola-io-%d", id_);
     pthread_setname_np(pthread_self(), name);
     loop_.refresh_clock();
+    if (options_.io_backend == IoBackend::kUring) uring_active_.store(loop_.enable_uring(), std::memory_order_relaxed);
     app_->on_worker_start(*this);
     if (listen_fd_ >= 0) loop_.add(listen_fd_, EPOLLIN, this);
     loop_.set_spin_ns(static_cast<int64_t>(options_.spin_us) * 1000);
@@ -556,6 +770,10 @@ void Worker::thread_main() {
         if (c->fd_ >= 0) {
             close(c->fd_);
             c->fd_ = -1;
+        }
+        if (c->zombie_fd_ >= 0) {
+            close(c->zombie_fd_);
+            c->zombie_fd_ = -1;
         }
     }
     app_->on_worker_exit(*this);
@@ -669,6 +887,14 @@ ServerStats Server::stats() const {
         }
     }
     return s;
+}
+
+const char* Server::io_backend_name() const {
+    if (options_.io_backend != IoBackend::kUring) return "epoll";
+    for (const auto& w : workers_) {
+        if (!w->uring_active_.load(std::memory_order_relaxed)) return "epoll";
+    }
+    return "uring";
 }
 
 std::vector<WorkerSnapshot> Server::worker_stats() const {

@@ -65,12 +65,13 @@ class Application {
     virtual void on_connection_closed(Worker& /*worker*/, ConnRef /*ref*/) {}
 };
 
-class Connection final : public EventHandler {
+class Connection final : public EventHandler, public UringHandler {
  public:
     explicit Connection(Worker* worker, uint32_t index) : worker_(worker), index_(index) {}
     ~Connection() override;
 
-    void on_events(uint32_t events) override;
+    void on_events(uint32_t events) override;                                                      // epoll backend
+    void on_completion(uint32_t tag, int32_t res, uint32_t cqe_flags, const char* data) override;  // io_uring backend
 
     std::string& out() { return out_; }
     // The response being appended is the last one on this connection.
@@ -90,6 +91,15 @@ class Connection final : public EventHandler {
     void update_interest();
     bool discard_body_bytes();
     bool input_full() const;  // buffer at its limit with nothing consumable (a deferred request and a greedy pipeliner)
+    bool output_pending() const {  // bytes owed to the peer that have not been handed to the kernel yet
+        return out_sent_ < out_.size() || send_inflight_ || sending_sent_ < sending_.size();
+    }
+    // io_uring backend (see the comment on IoBackend).
+    void uring_arm_recv();
+    void uring_cancel_recv();
+    void uring_submit_send();
+    void uring_input(const char* data, size_t len);
+    void uring_reap_zombie();
 
     Worker* worker_;
     const uint32_t index_;
@@ -114,6 +124,18 @@ class Connection final : public EventHandler {
     std::unique_ptr<ChunkedDecoder> discard_chunked_;
     uint32_t registered_events_ = 0;
     int64_t last_active_ns_ = 0;
+
+    // io_uring backend state.
+    bool uring_ = false;
+    int uring_slot_ = -1;           // handler slot in the loop, kept for the life of the object
+    bool recv_armed_ = false;       // a multishot receive is in flight
+    bool recv_cancelling_ = false;  // ... and has been asked to stop (back-pressure)
+    bool send_inflight_ = false;
+    bool zombie_ = false;           // closed, but completions of its last operations are still to come
+    int ops_ = 0;                   // operations in flight (receive, send, cancel)
+    int zombie_fd_ = -1;
+    std::string sending_;           // the bytes of the send in flight (must not move until it completes)
+    size_t sending_sent_ = 0;
 };
 
 enum class AcceptMode : uint8_t {
@@ -122,6 +144,17 @@ enum class AcceptMode : uint8_t {
     kRoundRobin,  // worker 0 accepts and deals connections in turn; no SO_REUSEPORT
 };
 
+// How sockets are driven.
+//   kEpoll  readiness: epoll_wait, then one recv and one send system call per request - the
+//           pattern of the reference's container (Undertow/XNIO, /root/reference/pom.xml:122-129).
+//   kUring  completion: one multishot receive per connection delivering into buffers the kernel
+//           picks from a shared pool, sends queued as submissions, and a single io_uring_enter per
+//           loop iteration that submits the batch and waits for the next completions. Listeners,
+//           timers, the mailbox and the outbound client stay on epoll, which is polled through the
+//           ring. Falls back to kEpoll when the kernel refuses io_uring. A closed connection keeps
+//           its slot until the completions of its last operations have arrived.
+enum class IoBackend : uint8_t { kEpoll, kUring };
+
 struct ServerOptions {
     std::string bind_address = "0.0.0.0";
     uint16_t port = 8080;
@@ -129,6 +162,7 @@ struct ServerOptions {
     int backlog = 1024;
     size_t max_header_bytes = 65536;  // request line + headers
     AcceptMode accept_mode = AcceptMode::kBalanced;
+    IoBackend io_backend = IoBackend::kEpoll;
     std::vector<int> cpu_affinity;    // optional: worker i is pinned to cpu_affinity[i % size]
     int shutdown_grace_ms = 5000;     // in-flight work gets this long to finish after SIGTERM
     int drain_linger_ms = 100;        // idle keep-alive connections stay answerable this long (see begin_drain)
@@ -222,6 +256,7 @@ class Worker final : public EventHandler {
     std::string canonical_path_;  // scratch for the request being dispatched
     void* app_state_ = nullptr;
     std::atomic<double> cpu_seconds_{0};  // filled in when the thread exits
+    std::atomic<bool> uring_active_{false};
     std::thread thread_;
 };
 
@@ -239,6 +274,8 @@ class Server {
     int threads() const { return static_cast<int>(workers_.size()); }
     ServerStats stats() const;
     std::vector<WorkerSnapshot> worker_stats() const;
+    // "epoll" or "uring": what the workers actually run on (uring falls back when refused).
+    const char* io_backend_name() const;
     Worker& worker(int i) { return *workers_[static_cast<size_t>(i)]; }
 
  private:

@@ -2,11 +2,12 @@
 // benchmark images): one ring, a provided-buffer ring for multishot receives, submission and
 // completion queues accessed with the acquire/release pairs the kernel ABI asks for.
 //
-// Used by the I/O-ceiling probe (src/tools/null_server.cc) to answer one question with a
-// measurement instead of an argument: how much of the per-request kernel time of the epoll +
-// recv + send path (/root/reference gets the same three calls from Undertow/XNIO,
-// /root/reference/pom.xml:122-129) is system-call and readiness-notification overhead that a
-// completion-based interface removes, and how much is TCP/loopback protocol work that stays.
+// Used by the I/O-ceiling probe (src/tools/null_server.cc) and by the server's optional
+// completion-based backend (--io-backend uring, src/net/event_loop.cc and server.cc). The
+// question behind both: how much of the per-request kernel time of the epoll + recv + send path
+// (/root/reference gets the same three calls from Undertow/XNIO, /root/reference/pom.xml:122-129)
+// is system-call and readiness-notification overhead that a completion-based interface removes,
+// and how much is TCP/loopback protocol work that stays.
 #pragma once
 
 #include <linux/io_uring.h>
@@ -91,6 +92,25 @@ class Uring {
         __atomic_store_n(sq_tail_, local_tail_, __ATOMIC_RELEASE);
         if (to_submit == 0 && wait_for == 0) return 0;
         const long r = syscall(__NR_io_uring_enter, fd_, to_submit, wait_for, IORING_ENTER_GETEVENTS, nullptr, 0);
+        return r < 0 ? -errno : 0;
+    }
+
+    // As submit_and_wait(1), but gives up after `timeout_ns` (0: do not wait at all, just submit
+    // and let the kernel post what has completed). Returns 0, -ETIME or another -errno.
+    int submit_and_wait_for(int64_t timeout_ns) {
+        const unsigned to_submit = local_tail_ - *sq_tail_;
+        __atomic_store_n(sq_tail_, local_tail_, __ATOMIC_RELEASE);
+        if (timeout_ns <= 0) {
+            const long r = syscall(__NR_io_uring_enter, fd_, to_submit, 0, IORING_ENTER_GETEVENTS, nullptr, 0);
+            return r < 0 ? -errno : 0;
+        }
+        __kernel_timespec ts;
+        ts.tv_sec = timeout_ns / 1000000000ll;
+        ts.tv_nsec = timeout_ns % 1000000000ll;
+        io_uring_getevents_arg arg;
+        std::memset(&arg, 0, sizeof arg);
+        arg.ts = reinterpret_cast<uint64_t>(&ts);
+        const long r = syscall(__NR_io_uring_enter, fd_, to_submit, 1, IORING_ENTER_GETEVENTS | IORING_ENTER_EXT_ARG, &arg, sizeof arg);
         return r < 0 ? -errno : 0;
     }
 

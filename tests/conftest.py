@@ -49,6 +49,8 @@ def pytest_addoption(parser):
     parser.addoption("--variant", default="release", choices=["release", "asan", "tsan", "static", "cov"],
                      help="which build of the hola executable the black-box tests launch "
                           "(asan: AddressSanitizer+UBSan, tsan: ThreadSanitizer; SURVEY.md 5.2)")
+    parser.addoption("--io-backend", default="epoll", choices=["epoll", "uring"],
+                     help="run every launched server with this --io-backend (uring: the io_uring backend of src/net/server.cc)")
 
 
 _deselected = {"count": 0}
@@ -85,6 +87,7 @@ def hola_server(request):
     the test if the sanitizer reported anything or the process did not exit cleanly.
     """
     variant = request.config.getoption("--variant")
+    io_backend = request.config.getoption("--io-backend")
     if variant != "release":
         hola_b200.build(variant)
     started: List[HolaServer] = []
@@ -98,6 +101,8 @@ def hola_server(request):
             merged["TSAN_OPTIONS"] = "halt_on_error=0:exitcode=66:second_deadlock_stack=1"
         merged.update(env or {})
         kw.setdefault("start_timeout", 10.0 if variant == "release" else 30.0)
+        if io_backend != "epoll" and "--io-backend" not in list(args):
+            args = list(args) + ["--io-backend", io_backend]
         srv = HolaServer(args=args, env=merged, threads=threads, variant=variant, **kw).start()
         started.append(srv)
         return srv

@@ -94,6 +94,10 @@ def main() -> int:
         ("hola (tracing off)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet"], base_env),
         ("hola (as-is)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet"],
          dict(base_env, ZIPKIN_SERVER_URL="http://127.0.0.1:9")),
+        ("hola uring (tracing off)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet",
+                                                "--io-backend", "uring"], base_env),
+        ("hola uring (as-is)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet",
+                                          "--io-backend", "uring"], dict(base_env, ZIPKIN_SERVER_URL="http://127.0.0.1:9")),
         ("null epoll", lambda p: [str(bin_dir / "hola-null"), "--port", str(p), "--threads", str(n_server), "--cpus", cpu_arg, "--io-backend", "epoll"], base_env),
         ("null uring", lambda p: [str(bin_dir / "hola-null"), "--port", str(p), "--threads", str(n_server), "--cpus", cpu_arg, "--io-backend", "uring"], base_env),
     ]
@@ -104,10 +108,10 @@ def main() -> int:
             try:
                 r = one(label, make_cmd(port), env, port, a.seconds, load_cpus, "/api/hola")
             except Exception as exc:  # noqa: BLE001
-                print("%-20s failed: %s" % (label, exc), flush=True)
+                print("%-26s failed: %s" % (label, exc), flush=True)
                 continue
             runs[label].append(r)
-            print("%-20s %9.0f req/s  p50 %5.1f us  p99 %6.1f us  user %.2f  sys %.2f us/req" %
+            print("%-26s %9.0f req/s  p50 %5.1f us  p99 %6.1f us  user %.2f  sys %.2f us/req" %
                   (label, r["rps"], r["p50_us"], r["p99_us"], r["user_us_per_req"], r["sys_us_per_req"]), flush=True)
     summary = {}
     for label, rs in runs.items():
@@ -115,10 +119,14 @@ def main() -> int:
             summary[label] = {k: round(statistics.median(r[k] for r in rs), 3) for k in ("rps", "p50_us", "p99_us", "user_us_per_req", "sys_us_per_req")}
     ratios = {}
     if "null epoll" in summary:
-        for label in ("hola (tracing off)", "hola (as-is)", "null uring"):
+        for label in ("hola (tracing off)", "hola (as-is)", "hola uring (tracing off)", "hola uring (as-is)", "null uring"):
             if label in summary:
                 ratios[label + " / null epoll"] = round(summary[label]["rps"] / summary["null epoll"]["rps"], 3)
     doc = {"server_cpus": server_cpus, "load_cpus": load_cpus, "seconds": a.seconds, "repeat": a.repeat, "median": summary, "ratios": ratios, "runs": runs}
+    for a_label, b_label in (("hola uring (tracing off)", "hola (tracing off)"), ("hola uring (as-is)", "hola (as-is)")):
+        if a_label in summary and b_label in summary:
+            ratios[a_label + " / " + b_label] = round(summary[a_label]["rps"] / summary[b_label]["rps"], 3)
+            ratios["p99: " + a_label + " / " + b_label] = round(summary[a_label]["p99_us"] / summary[b_label]["p99_us"], 3)
     print(json.dumps({"median": summary, "ratios": ratios}, indent=1))
     if a.out:
         Path(a.out).parent.mkdir(parents=True, exist_ok=True)
