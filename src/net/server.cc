@@ -213,12 +213,8 @@ void Connection::on_completion(uint32_t tag, int32_t res, uint32_t cqe_flags, co
             if (res > 0) {
                 if (data) uring_input(data, static_cast<size_t>(res));
             } else if (res == 0) {
-                peer_closed_ = true;
-                if (streaming_ || (!deferred_ && !output_pending())) {
-                    close_now();
-                    return;
-                }
-                close_after_write_ = true;  // finish what is owed, then close
+                on_peer_closed();
+                if (fd_ < 0) return;
             } else if (res != -ENOBUFS && res != -ECANCELED && res != -EINTR && res != -EAGAIN) {
                 close_now();
                 return;
@@ -339,13 +335,7 @@ void Connection::on_events(uint32_t events) {
             continue;
         }
         if (n == 0) {
-            peer_closed_ = true;
-            if (streaming_ || (!deferred_ && out_sent_ >= out_.size())) {
-                close_now();
-            } else {
-                close_after_write_ = true;  // finish what is owed, then close
-                update_interest();
-            }
+            on_peer_closed();
             return;
         }
         if (errno == EINTR) continue;
@@ -353,6 +343,19 @@ void Connection::on_events(uint32_t events) {
         close_now();
         return;
     }
+}
+
+// The peer has sent its FIN: no further request will come, but everything received so far is
+// still owed an answer - including requests that sit unparsed in the buffer behind a deferred
+// one (a client may pipeline a batch and half-close at once).
+void Connection::on_peer_closed() {
+    peer_closed_ = true;
+    if (streaming_ || (!deferred_ && !output_pending())) {
+        close_now();  // not deferred: every complete request in the buffer has been parsed and answered already
+        return;
+    }
+    if (!deferred_) close_after_write_ = true;  // what is being written is the last answer
+    update_interest();
 }
 
 bool Connection::discard_body_bytes() {
@@ -435,6 +438,9 @@ void Connection::process_input() {
         }
     }
     in_process_ = false;
+    // Everything the peer sent before its FIN has been parsed now (what is left, if anything, is
+    // a fragment that will never be completed): the answers being flushed are the last ones.
+    if (fd_ >= 0 && peer_closed_ && !deferred_ && !streaming_) close_after_write_ = true;
     flush();
 }
 
@@ -673,7 +679,7 @@ bool Worker::complete(ConnRef ref, std::string_view response, bool close_after) 
     if (!c || !c->deferred_) return false;
     c->deferred_ = false;
     c->out_.append(response);
-    if (close_after || c->peer_closed_ || draining_) c->close_after_write_ = true;
+    if (close_after || draining_) c->close_after_write_ = true;  // a half-closed peer: process_input() decides once the buffer is drained
     c->process_input();  // resumes parsing of pipelined requests, then flushes
     return true;
 }

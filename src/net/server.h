@@ -90,6 +90,7 @@ class Connection final : public EventHandler, public UringHandler {
     void flush();
     void update_interest();
     bool discard_body_bytes();
+    void on_peer_closed();
     bool input_full() const;  // buffer at its limit with nothing consumable (a deferred request and a greedy pipeliner)
     bool output_pending() const {  // bytes owed to the peer that have not been handed to the kernel yet
         return out_sent_ < out_.size() || send_inflight_ || sending_sent_ < sending_.size();

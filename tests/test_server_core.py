@@ -372,6 +372,32 @@ def test_deferred_request_with_full_buffer_and_half_closed_peer_does_not_spin(ho
     c.close()
 
 
+def test_half_close_behind_a_deferred_request_keeps_the_pipelined_requests(hola_server, fake_aloha):
+    """A client writes a batch - the first request needs the downstream call, the rest are queued
+    behind it - and half-closes straight away. The FIN reaches the server while the first request
+    is still pending; the queued requests were sent before it and must all be answered."""
+    fake_aloha.delay = 0.3
+    srv = hola_server(args=["--aloha-url", fake_aloha.url], threads=1)
+    c = client.Connection("127.0.0.1", srv.port, timeout=10)
+    c.send_raw(client.build_request("GET", "/api/hola-chaining") + client.build_request("GET", "/api/hola") * 3 +
+               client.build_request("GET", "/api/health"))
+    c.sock.shutdown(socket.SHUT_WR)
+    assert c.read_response().body.startswith(b'["Hola de unknown","Aloha mai')
+    for _ in range(3):
+        assert c.read_response().body == HOLA
+    assert c.read_response().body == b"I'm ok"
+    assert c.closed_by_peer()
+    c.close()
+    # ... and the plain case: a batch and a FIN with nothing deferred.
+    c = client.Connection("127.0.0.1", srv.port, timeout=10)
+    c.send_raw(client.build_request("GET", "/api/hola") * 5)
+    c.sock.shutdown(socket.SHUT_WR)
+    for _ in range(5):
+        assert c.read_response().body == HOLA
+    assert c.closed_by_peer()
+    c.close()
+
+
 def test_connection_slot_is_not_reused_within_one_batch_of_events(hola_server, fake_aloha):
     """One worker, stopped with SIGSTOP while three things queue up in this order: the downstream
     reply for deferred connection A, a new client B, and a reset of A. On resume the reply cannot
