@@ -91,10 +91,10 @@ def mode_settings(mode: str):
     return env, args, expect
 
 
-def make_server(impl: str, mode: str, server_cpus: Sequence[int], threads: int, io_backend: str = "epoll"):
+def make_server(impl: str, mode: str, server_cpus: Sequence[int], threads: int, io_backend: str = "auto"):
     """The process under test: this repository's executable, or the reference (hola_b200/reference.py)."""
     env, args, _ = mode_settings(mode)
-    if io_backend != "epoll":
+    if io_backend != "auto":
         args = args + ["--io-backend", io_backend]
     if impl == "reference":
         from hola_b200.reference import ReferenceServer, reference_command
@@ -137,7 +137,7 @@ def coldstart_ms(impl: str, mode: str, runs: int = 5) -> Optional[Dict]:
 
 
 def run_instance(index: int, cpus: Sequence[int], steps: int, warmup: int, mode: str, impl: str, results: Dict[int, Dict],
-                 half_load_seconds: int = 0, io_backend: str = "epoll") -> None:
+                 half_load_seconds: int = 0, io_backend: str = "auto") -> None:
     from hola_b200 import loadgen
 
     cpus = list(cpus)
@@ -199,8 +199,9 @@ def main() -> int:
                     help="after the timed run (N=1 only): an open-loop run at half the measured rate for this many "
                          "seconds, reported as `half_load` (0 to skip)")
     ap.add_argument("--coldstart-runs", type=int, default=5, help="launches for `coldstart_ms` (0 to skip)")
-    ap.add_argument("--io-backend", choices=["epoll", "uring"], default=os.environ.get("HOLA_BENCH_IO_BACKEND", "epoll"),
-                    help="the service's --io-backend (ours only)")
+    ap.add_argument("--io-backend", choices=["auto", "epoll", "uring"], default=os.environ.get("HOLA_BENCH_IO_BACKEND", "auto"),
+                    help="the service's --io-backend (ours only; auto is the service's default: io_uring where the kernel "
+                         "offers it, else epoll - what was used is reported as config.io_backend)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3  # timing rule: W >= 3

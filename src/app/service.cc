@@ -34,9 +34,10 @@ std::string usage_text() {
            "  --accept-mode MODE          balanced (default: a listener per thread, new connections go to the least-loaded\n"
            "                              thread) | reuseport (a listener per thread, the kernel's hash decides) |\n"
            "                              rr (one acceptor deals connections in turn; no SO_REUSEPORT)\n"
-           "  --io-backend BACKEND        epoll (default: readiness, one recv and one send per request) | uring (io_uring:\n"
+           "  --io-backend BACKEND        epoll (readiness: one recv and one send system call per request) | uring (io_uring:\n"
            "                              multishot receives into kernel-picked buffers, sends batched into one system call\n"
-           "                              per loop iteration; falls back to epoll where the kernel refuses it)\n"
+           "                              per loop iteration; needs Linux 6.1+, says so and uses epoll where refused) |\n"
+           "                              auto (default: uring where available, else epoll, silently)\n"
            "  --aloha-url URL             downstream base URL (default http://aloha:8080/)\n"
            "  --feign-max-attempts N      tries per downstream call on connection failures (default 5, as Feign's\n"
            "                              default Retryer: pauses of 150, 225, 337, 506 ms; 1 disables retrying)\n"
@@ -123,8 +124,8 @@ ParseOutcome parse_service_args(const std::vector<std::string>& args, ServiceCon
             if (!value(&v) || (v != "balanced" && v != "reuseport" && v != "rr")) return fail("--accept-mode is balanced, reuseport or rr");
             cfg->server.accept_mode = v == "balanced" ? AcceptMode::kBalanced : v == "reuseport" ? AcceptMode::kReusePort : AcceptMode::kRoundRobin;
         } else if (a == "--io-backend") {
-            if (!value(&v) || (v != "epoll" && v != "uring")) return fail("--io-backend is epoll or uring");
-            cfg->server.io_backend = v == "uring" ? IoBackend::kUring : IoBackend::kEpoll;
+            if (!value(&v) || (v != "auto" && v != "epoll" && v != "uring")) return fail("--io-backend is auto, epoll or uring");
+            cfg->server.io_backend = v == "uring" ? IoBackend::kUring : v == "epoll" ? IoBackend::kEpoll : IoBackend::kAuto;
         } else if (a == "--aloha-url") {
             std::string host, path;
             uint16_t port = 80;
@@ -313,9 +314,9 @@ bool Service::start(std::string* error) {
     tracer_->start();
     started_ = true;
     char msg[256];
-    std::snprintf(msg, sizeof msg, "hola %s listening on %s:%u with %d thread(s), started in %.1f ms%s", HOLA_VERSION,
+    std::snprintf(msg, sizeof msg, "hola %s listening on %s:%u with %d thread(s), started in %.1f ms, %s%s", HOLA_VERSION,
                   config_.server.bind_address.c_str(), server_->port(), server_->threads(),
-                  static_cast<double>(monotonic_ns() - t_start) / 1e6, tracer_->enabled() ? ", tracing on" : "");
+                  static_cast<double>(monotonic_ns() - t_start) / 1e6, server_->io_backend_name(), tracer_->enabled() ? ", tracing on" : "");
     log("INFO", msg);
     return true;
 }

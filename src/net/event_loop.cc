@@ -150,12 +150,12 @@ void EventLoop::dispatch_epoll(int n, epoll_event* events) {
 
 // ---- completion-based mode --------------------------------------------------------------------
 
-bool EventLoop::enable_uring(unsigned entries, unsigned buffers, unsigned buffer_size) {
+bool EventLoop::enable_uring(bool quiet, unsigned entries, unsigned buffers, unsigned buffer_size) {
     std::unique_ptr<Uring> ring(new Uring());
-    int rc = ring->init(entries);
+    int rc = ring->init(entries, /*modern_only=*/true);
     if (rc == 0) rc = ring->setup_buffers(1, buffers, buffer_size);
     if (rc != 0) {
-        std::fprintf(stderr, "hola: io_uring is not usable here (%s) - staying with epoll\n", std::strerror(-rc));
+        if (!quiet) std::fprintf(stderr, "hola: io_uring is not usable here (%s) - staying with epoll\n", std::strerror(-rc));
         return false;
     }
     uring_ = std::move(ring);

@@ -89,13 +89,15 @@ class EventLoop {
     bool stopping() const { return stop_.load(std::memory_order_relaxed); }
 
     // Completion-based I/O. enable_uring() must be called on the loop's own thread before run();
-    // it returns false (and the loop stays a plain epoll loop) when the kernel refuses. In uring
+    // it returns false (and the loop stays a plain epoll loop) when the kernel refuses - io_uring
+    // compiled out or switched off (kernel.io_uring_disabled), blocked by a seccomp profile as in
+    // many container runtimes, or older than Linux 6.1. In uring
     // mode the epoll set is still served - it is polled through the ring - so listeners, the
     // mailbox and the outbound client work unchanged; sockets that want completions register a
     // UringHandler and submit their own receives and sends:
     //     sqe = loop.uring_sqe(); fill it; sqe->user_data = loop.uring_user_data(slot, tag);
     // Submissions are flushed once per loop iteration, together with the wait for completions.
-    bool enable_uring(unsigned entries = 4096, unsigned buffers = 1024, unsigned buffer_size = 4096);
+    bool enable_uring(bool quiet = false, unsigned entries = 1024, unsigned buffers = 512, unsigned buffer_size = 4096);
     bool uring_enabled() const { return uring_ != nullptr; }
     int register_uring_handler(UringHandler* h);
     static uint64_t uring_user_data(int slot, uint32_t tag) { return (static_cast<uint64_t>(slot + 1) << 32) | tag; }

@@ -762,7 +762,10 @@ void Worker::thread_main() {
     std::snprintf(name, sizeof name, "hola-io-%d", id_);
     pthread_setname_np(pthread_self(), name);
     loop_.refresh_clock();
-    if (options_.io_backend == IoBackend::kUring) uring_active_.store(loop_.enable_uring(), std::memory_order_relaxed);
+    if (options_.io_backend != IoBackend::kEpoll) {
+        uring_active_.store(loop_.enable_uring(/*quiet=*/options_.io_backend == IoBackend::kAuto), std::memory_order_relaxed);
+    }
+    backend_decided_.store(true, std::memory_order_release);
     app_->on_worker_start(*this);
     if (listen_fd_ >= 0) loop_.add(listen_fd_, EPOLLIN, this);
     loop_.set_spin_ns(static_cast<int64_t>(options_.spin_us) * 1000);
@@ -896,8 +899,9 @@ ServerStats Server::stats() const {
 }
 
 const char* Server::io_backend_name() const {
-    if (options_.io_backend != IoBackend::kUring) return "epoll";
+    if (options_.io_backend == IoBackend::kEpoll) return "epoll";
     for (const auto& w : workers_) {
+        while (!w->backend_decided_.load(std::memory_order_acquire)) std::this_thread::yield();  // the first thing a worker does
         if (!w->uring_active_.load(std::memory_order_relaxed)) return "epoll";
     }
     return "uring";

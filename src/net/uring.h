@@ -29,14 +29,17 @@ class Uring {
     ~Uring() { close_ring(); }
 
     // Returns 0 or -errno. The ring is meant for one thread: it asks for SINGLE_ISSUER and
-    // DEFER_TASKRUN (completions are only posted when this thread enters the kernel to wait),
-    // falling back to a plain ring on kernels that refuse the flags.
-    int init(unsigned entries) {
+    // DEFER_TASKRUN (completions are only posted when this thread enters the kernel to wait).
+    // A kernel that refuses those flags is older than 6.1; with `modern_only` that is an error
+    // (-ENOSYS) - such a kernel may lack multishot receives and buffer rings too, which cannot
+    // be probed for directly - otherwise a plain ring is tried.
+    int init(unsigned entries, bool modern_only = false) {
         io_uring_params p;
         std::memset(&p, 0, sizeof p);
         p.flags = IORING_SETUP_SINGLE_ISSUER | IORING_SETUP_DEFER_TASKRUN | IORING_SETUP_CQSIZE | IORING_SETUP_CLAMP;
         p.cq_entries = entries * 4;
         int fd = static_cast<int>(syscall(__NR_io_uring_setup, entries, &p));
+        if (fd < 0 && modern_only) return errno == EINVAL ? -ENOSYS : -errno;
         if (fd < 0) {
             std::memset(&p, 0, sizeof p);
             p.flags = IORING_SETUP_CQSIZE | IORING_SETUP_CLAMP;
@@ -131,7 +134,9 @@ class Uring {
         const size_t ring_bytes = count * sizeof(io_uring_buf);
         buf_ring_ = static_cast<io_uring_buf_ring*>(mmap(nullptr, ring_bytes, PROT_READ | PROT_WRITE, MAP_ANONYMOUS | MAP_PRIVATE | MAP_POPULATE, -1, 0));
         if (buf_ring_ == MAP_FAILED) return -errno;
-        buf_mem_ = static_cast<char*>(mmap(nullptr, static_cast<size_t>(count) * size, PROT_READ | PROT_WRITE, MAP_ANONYMOUS | MAP_PRIVATE | MAP_POPULATE, -1, 0));
+        // Not pre-faulted: the pages are touched when the kernel first delivers into them, which
+        // keeps start-up short (4 MB of page faults would cost over a millisecond per thread).
+        buf_mem_ = static_cast<char*>(mmap(nullptr, static_cast<size_t>(count) * size, PROT_READ | PROT_WRITE, MAP_ANONYMOUS | MAP_PRIVATE, -1, 0));
         if (buf_mem_ == MAP_FAILED) return -errno;
         io_uring_buf_reg reg;
         std::memset(&reg, 0, sizeof reg);

@@ -49,8 +49,9 @@ def pytest_addoption(parser):
     parser.addoption("--variant", default="release", choices=["release", "asan", "tsan", "static", "cov"],
                      help="which build of the hola executable the black-box tests launch "
                           "(asan: AddressSanitizer+UBSan, tsan: ThreadSanitizer; SURVEY.md 5.2)")
-    parser.addoption("--io-backend", default="epoll", choices=["epoll", "uring"],
-                     help="run every launched server with this --io-backend (uring: the io_uring backend of src/net/server.cc)")
+    parser.addoption("--io-backend", default="auto", choices=["auto", "epoll", "uring"],
+                     help="run every launched server with this --io-backend (auto, the service's default: io_uring where the "
+                          "kernel offers it, else epoll). test_server_core.py and test_chaining.py always run on both.")
 
 
 _deselected = {"count": 0}
@@ -101,8 +102,9 @@ def hola_server(request):
             merged["TSAN_OPTIONS"] = "halt_on_error=0:exitcode=66:second_deadlock_stack=1"
         merged.update(env or {})
         kw.setdefault("start_timeout", 10.0 if variant == "release" else 30.0)
-        if io_backend != "epoll" and "--io-backend" not in list(args):
-            args = list(args) + ["--io-backend", io_backend]
+        backend = os.environ.get("HOLA_TEST_IO_BACKEND") or io_backend  # see `both_io_backends`
+        if backend != "auto" and "--io-backend" not in list(args):
+            args = list(args) + ["--io-backend", backend]
         srv = HolaServer(args=args, env=merged, threads=threads, variant=variant, **kw).start()
         started.append(srv)
         return srv
@@ -115,6 +117,16 @@ def hola_server(request):
             if code not in (0, None) or "Sanitizer" in srv.stderr or "runtime error:" in srv.stderr:
                 problems.append("exit %s\n%s" % (code, srv.stderr[-6000:]))
     assert not problems, "sanitizer findings:\n" + "\n----\n".join(problems)
+
+
+@pytest.fixture(params=["epoll", "uring"])
+def both_io_backends(request, monkeypatch):
+    """Runs the requesting test twice: once with `--io-backend epoll`, once with `uring` (which
+    is epoll again on a kernel without a usable io_uring - the service says so on stderr).
+    Modules that exercise the connection state machine opt in with
+    ``pytestmark = pytest.mark.usefixtures("both_io_backends")``."""
+    monkeypatch.setenv("HOLA_TEST_IO_BACKEND", request.param)
+    return request.param
 
 
 from hola_b200.fakes import FakeAloha, FakeZipkin  # noqa: E402,F401

@@ -5,7 +5,12 @@ from __future__ import annotations
 import json
 import time
 
+import pytest
+
 from hola_b200 import client
+
+# The connection state machine has two I/O backends (src/net/server.h, IoBackend): every test here runs on both.
+pytestmark = pytest.mark.usefixtures("both_io_backends")
 
 FALLBACK = "Aloha response (fallback)"
 

@@ -10,6 +10,9 @@ import pytest
 
 from hola_b200 import client
 
+# The connection state machine has two I/O backends (src/net/server.h, IoBackend): every test here runs on both.
+pytestmark = pytest.mark.usefixtures("both_io_backends")
+
 HOLA = b"Hola de unknown"
 
 

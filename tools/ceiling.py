@@ -4,7 +4,8 @@
 Runs the identical hola-load configuration (64 keep-alive connections, closed loop, bodies
 verified, same pinning as bench.py) against
 
-  * `hola`                        the service (tracing off and as-is),
+  * `hola --io-backend epoll`     the service on its readiness backend (tracing off and as-is),
+  * `hola --io-backend uring`     the service on its io_uring backend,
   * `hola-null --io-backend epoll`  recv -> canned 200 -> send with hola's threading: no parsing at all,
   * `hola-null --io-backend uring`  the same probe on io_uring (multishot recv, batched sends),
 
@@ -91,9 +92,10 @@ def main() -> int:
     bin_dir = paths().hola.parent
     base_env = {k: v for k, v in os.environ.items() if k not in ("HOSTNAME", "ZIPKIN_SERVER_URL")}
     variants = [
-        ("hola (tracing off)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet"], base_env),
-        ("hola (as-is)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet"],
-         dict(base_env, ZIPKIN_SERVER_URL="http://127.0.0.1:9")),
+        ("hola (tracing off)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet",
+                                          "--io-backend", "epoll"], base_env),
+        ("hola (as-is)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet",
+                                    "--io-backend", "epoll"], dict(base_env, ZIPKIN_SERVER_URL="http://127.0.0.1:9")),
         ("hola uring (tracing off)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet",
                                                 "--io-backend", "uring"], base_env),
         ("hola uring (as-is)", lambda p: [str(bin_dir / "hola"), "--port", str(p), "--bind", "127.0.0.1", "--threads", str(n_server), "--cpus", cpu_arg, "--quiet",
