@@ -19,9 +19,13 @@ _lib: Optional[ctypes.CDLL] = None
 def lib() -> ctypes.CDLL:
     global _lib
     if _lib is None:
-        p = paths().libhola
+        # HOLA_LIB_VARIANT=cov|asan|tsan loads the library of that build (tools/coverage.sh counts
+        # the lines the C-ABI tests reach that way).
+        import os
+        variant = os.environ.get("HOLA_LIB_VARIANT", "release")
+        p = paths(variant).libhola
         if not p.exists():
-            build()
+            build(variant)
         _lib = ctypes.CDLL(str(p))
         _declare(_lib)
     return _lib

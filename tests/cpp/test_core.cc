@@ -197,7 +197,94 @@ TEST(format_rejections) {
     CHECK(fmt_fails("%s %q", "UnknownFormatConversionException"));  // parse errors win over everything
 }
 
+// ---- text --------------------------------------------------------------------------------------
+
+TEST(text_utf8_edges) {
+    std::string out;
+    append_utf8(&out, 0x41);
+    append_utf8(&out, 0xE9);
+    append_utf8(&out, 0x20AC);
+    append_utf8(&out, 0x1F600);
+    CHECK_EQ(out, std::string("A\xC3\xA9\xE2\x82\xAC\xF0\x9F\x98\x80"));
+    out.clear();
+    append_utf8(&out, 0xD800);    // a lone surrogate has no UTF-8 form: the JVM writes '?'
+    append_utf8(&out, 0x110000);  // beyond Unicode
+    CHECK_EQ(out, std::string("??"));
+    // Malformed input decodes as U+FFFD, one byte at a time, and always advances.
+    const std::string bad[] = {"\x80", "\xC3", "\xC3\x41", "\xE2\x82", "\xE2\x41\x41", "\xF0\x9F\x98", "\xF8\x88\x80\x80\x80",
+                               "\xC0\x80" /* overlong NUL */, "\xE0\x80\x80" /* overlong */, "\xED\xA0\x80" /* surrogate */, "\xF4\x90\x80\x80" /* > U+10FFFF */};
+    for (const std::string& b : bad) {
+        size_t pos = 0;
+        CHECK_EQ(decode_utf8(b, &pos), uint32_t{0xFFFD});
+        CHECK_EQ(pos, size_t{1});
+    }
+    size_t pos = 0;
+    CHECK_EQ(decode_utf8("\xE2\x82\xAC", &pos), uint32_t{0x20AC});
+    CHECK_EQ(pos, size_t{3});
+    CHECK_EQ(utf16_length("a\xC3\xA9\xF0\x9F\x98\x80"), size_t{4});
+    CHECK_EQ(std::string(utf16_prefix("a\xF0\x9F\x98\x80z", 2)), std::string("a"));  // never half of a surrogate pair
+    CHECK_EQ(std::string(utf16_prefix("a\xF0\x9F\x98\x80z", 3)), std::string("a\xF0\x9F\x98\x80"));
+    // String.hashCode walks UTF-16 units: "\uD83D\uDE00".hashCode() == 0xD83D * 31 + 0xDE00.
+    CHECK_EQ(java_string_hash("\xF0\x9F\x98\x80"), static_cast<int32_t>(0xD83D * 31 + 0xDE00));
+}
+
+TEST(text_upper_case_like_the_jvm) {
+    CHECK_EQ(to_upper_java("hola de mar\xC3\xAD" "a"), std::string("HOLA DE MAR\xC3\x8D" "A"));
+    CHECK_EQ(to_upper_java("stra\xC3\x9F" "e"), std::string("STRASSE"));       // one-to-two
+    CHECK_EQ(to_upper_java("\xC3\xBF"), std::string("\xC5\xB8"));            // y with diaeresis leaves Latin-1: U+0178
+    CHECK_EQ(to_upper_java("\xC2\xB5"), std::string("\xCE\x9C"));            // micro sign -> Greek capital mu
+    CHECK_EQ(to_upper_java("\xC3\xB7 \xC3\x97"), std::string("\xC3\xB7 \xC3\x97"));  // division and multiplication signs have no case
+    CHECK_EQ(to_upper_java("\xD0\xB6"), std::string("\xD0\xB6"));            // other scripts are left alone (documented)
+}
+
+TEST(text_utf16_assembler_and_cpu_lists) {
+    std::string out;
+    Utf16Assembler a(&out);
+    a.push_unit(0xD83D);
+    a.push_unit(0xDE00);  // a pair: one astral character
+    a.push_unit(0xDE00);  // a low half on its own
+    a.push_unit(0xD83D);  // a high half followed by something else
+    a.push_unit(0x41);
+    a.push_unit(0xD83D);  // ... and one left over at the end
+    a.flush();
+    CHECK_EQ(out, std::string("\xF0\x9F\x98\x80?" "?A?"));
+    std::vector<int> cpus;
+    CHECK(parse_cpu_list("0,2,4-7", &cpus));
+    CHECK_EQ(cpus.size(), size_t{6});
+    CHECK_EQ(cpus[5], 7);
+    cpus.clear();
+    CHECK(parse_cpu_list("3,,4,", &cpus));  // empty items are skipped
+    CHECK_EQ(cpus.size(), size_t{2});
+    for (const char* bad : {"", ",", "a", "1-", "-1", "5-2", "1-2-3", "1234567", "0x3"}) {
+        cpus.clear();
+        CHECK(!parse_cpu_list(bad, &cpus));
+    }
+}
+
 // ---- json --------------------------------------------------------------------------------------
+
+TEST(json_escapes_and_malformed_documents) {
+    std::string out;
+    json_append_string(&out, std::string("q\" b\\ /\b\f\n\r\t\x01\x1f z"));
+    CHECK_EQ(out, std::string("\"q\\\" b\\\\ /\\b\\f\\n\\r\\t\\u0001\\u001F z\""));
+    JsonStringList items;
+    std::string err;
+    CHECK(json_decode_string_list("[\"\\\"\\\\\\/\\b\\f\\n\\r\\t\\u0041\\uD83D\\uDE00\"]", &items, &err));
+    CHECK_EQ(*items[0], std::string("\"\\/\b\f\n\r\tA\xF0\x9F\x98\x80"));
+    CHECK(json_decode_string_list(" [ 1 , -2.5e+3 , true , false , null , \"x\" ] ", &items, &err));
+    CHECK_EQ(items.size(), size_t{6});
+    CHECK_EQ(*items[1], std::string("-2.5e+3"));
+    CHECK(!items[4].has_value());
+    const char* bad[] = {"", "[", "[\"a\"", "[\"a\",]", "[,]", "{\"a\":1}", "[[1]]", "[{\"a\":1}]", "[\"a\" \"b\"]",
+                         "[\"\x01\"]", "[\"\\", "[\"\\u12\"]", "[\"\\u12G4\"]", "[\"\\q\"]", "[-]", "[1.]", "[1e]", "[01x]", "[tru]", "[nul]", "\"a\""};
+    CHECK(json_decode_string_list("[\"a\"] trailing", &items, &err));  // Jackson's readValue stops after the first value
+    for (const char* doc : bad) {
+        err.clear();
+        if (json_decode_string_list(doc, &items, &err)) std::fprintf(stderr, "  accepted: %s\n", doc);
+        CHECK(!json_decode_string_list(doc, &items, &err));
+        CHECK(!err.empty());
+    }
+}
 
 TEST(json_encode) {
     CHECK_EQ(json_encode_string_list({}), std::string("[]"));

@@ -8,10 +8,12 @@ make cov -j"$(nproc)" > /dev/null
 find build/cov -name '*.gcda' -delete
 ./build/cov/hola_tests > /dev/null
 python -m pytest tests/test_contract.py tests/test_server_core.py tests/test_chaining.py tests/test_tracing.py \
-    tests/test_stream.py tests/test_dns.py tests/test_fuzz.py -q --variant cov -p no:cacheprovider > /dev/null
+    tests/test_stream.py tests/test_dns.py tests/test_fuzz.py tests/test_cli.py -q --variant cov -p no:cacheprovider > /dev/null
+# The building blocks through the C ABI (hypothesis tests), against the instrumented library.
+HOLA_LIB_VARIANT=cov python -m pytest tests/test_native_units.py -q -p no:cacheprovider > /dev/null
 out=profiles/coverage.txt
 {
-  echo "# gcov line coverage, $(date -u +%Y-%m-%d), C++ unit tests + black-box pytest against build/cov/hola"
+  echo "# gcov line coverage, $(date -u +%Y-%m-%d), C++ unit tests + black-box pytest against build/cov/hola + C-ABI tests against build/cov/libhola.so"
   printf '%-32s %8s %8s\n' file lines covered
   total=0; hit=0
   for src in src/core/*.cc src/net/*.cc src/app/*.cc; do
