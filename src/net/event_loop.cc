@@ -150,16 +150,21 @@ void EventLoop::dispatch_epoll(int n, epoll_event* events) {
 
 // ---- completion-based mode --------------------------------------------------------------------
 
-bool EventLoop::enable_uring(bool quiet, unsigned entries, unsigned buffers, unsigned buffer_size) {
-    std::unique_ptr<Uring> ring(new Uring());
-    int rc = ring->init(entries, /*modern_only=*/true);
+std::shared_ptr<Uring> EventLoop::prepare_uring(std::string* error, unsigned entries, unsigned buffers, unsigned buffer_size) {
+    std::shared_ptr<Uring> ring(new Uring());
+    int rc = ring->init(entries, /*modern_only=*/true, /*disabled=*/true);
     if (rc == 0) rc = ring->setup_buffers(1, buffers, buffer_size);
     if (rc != 0) {
-        if (!quiet) std::fprintf(stderr, "hola: io_uring is not usable here (%s) - staying with epoll\n", std::strerror(-rc));
-        return false;
+        if (error) *error = std::strerror(-rc);
+        return nullptr;
     }
+    return ring;
+}
+
+bool EventLoop::adopt_uring(std::shared_ptr<Uring> ring) {
+    if (uring_ || !ring || ring->enable() != 0) return false;
     uring_ = std::move(ring);
-    return true;
+    return true;  // run() notices at the end of this iteration and continues in run_uring()
 }
 
 int EventLoop::register_uring_handler(UringHandler* h) {
@@ -198,8 +203,9 @@ void EventLoop::run_uring() {
     constexpr int kMaxEvents = 256;
     epoll_event events[kMaxEvents];
     arm_epoll_poll();
+    bool epoll_backlog = true;  // whatever the epoll loop left pending when it handed over
     while (!stop_.load(std::memory_order_acquire)) {
-        const int timeout_ms = next_timeout_ms();
+        const int timeout_ms = epoll_backlog ? 0 : next_timeout_ms();
         if (timeout_ms != 0) ++stats_.blocking_waits;
         const int rc = uring_->submit_and_wait_for(static_cast<int64_t>(timeout_ms) * 1000000);
         refresh_clock();
@@ -231,9 +237,20 @@ void EventLoop::run_uring() {
             if (flags & IORING_CQE_F_BUFFER) uring_->recycle_buffer(bid, true);
         }
         last_event_ns_ = now_ns_;
-        if (epoll_ready) {
-            const int n = epoll_wait(epfd_, events, kMaxEvents, 0);
-            if (n > 0) dispatch_epoll(n, events);
+        if (epoll_ready || epoll_backlog) {
+            // The poll on the epoll descriptor reports *new* readiness only. The epoll set itself
+            // is level-triggered and its handlers rely on that (a short read leaves a pending FIN
+            // for the next round), so keep asking until nothing is ready; a descriptor that stays
+            // ready for several rounds is carried over to the next iteration, which then does not
+            // sleep - the same behaviour as the plain epoll loop, at the cost of one more
+            // epoll_wait(0) per batch of epoll activity (not on the path of io_uring sockets).
+            epoll_backlog = false;
+            for (int round = 0; round < 4; ++round) {
+                const int n = epoll_wait(epfd_, events, kMaxEvents, 0);
+                if (n <= 0) break;
+                dispatch_epoll(n, events);
+                if (round == 3) epoll_backlog = true;
+            }
         }
         run_timers();
         run_deferred();
@@ -284,6 +301,10 @@ void EventLoop::run() {
         dispatch_epoll(n, events);
         run_timers();
         run_deferred();
+        if (uring_) {  // adopt_uring() was called during this iteration
+            run_uring();
+            return;
+        }
     }
     run_deferred();  // left by an early exit from the loop
 }

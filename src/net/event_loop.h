@@ -16,6 +16,7 @@
 #include <memory>
 #include <mutex>
 #include <queue>
+#include <string>
 #include <unordered_map>
 #include <vector>
 
@@ -88,16 +89,22 @@ class EventLoop {
     void stop();  // safe from any thread
     bool stopping() const { return stop_.load(std::memory_order_relaxed); }
 
-    // Completion-based I/O. enable_uring() must be called on the loop's own thread before run();
-    // it returns false (and the loop stays a plain epoll loop) when the kernel refuses - io_uring
-    // compiled out or switched off (kernel.io_uring_disabled), blocked by a seccomp profile as in
-    // many container runtimes, or older than Linux 6.1. In uring
-    // mode the epoll set is still served - it is polled through the ring - so listeners, the
-    // mailbox and the outbound client work unchanged; sockets that want completions register a
-    // UringHandler and submit their own receives and sends:
+    // Completion-based I/O. A ring is made in two steps so that a loop never waits for one:
+    // prepare_uring() - any thread - creates it (disabled) and registers its buffers; creating
+    // rings is usually a matter of 0.1 ms but now and then the kernel takes 10-40 ms over one
+    // (measured, tools/uring_setup_probe.cc), which must not delay the first request.
+    // adopt_uring() - on the loop's own thread, e.g. posted to it - takes the ring over; the loop
+    // switches to it at the end of the current iteration. Sockets registered with epoll before
+    // that stay there: in uring mode the epoll set is still served - it is polled through the
+    // ring - so listeners, the mailbox and the outbound client work unchanged; sockets that want
+    // completions register a UringHandler and submit their own receives and sends:
     //     sqe = loop.uring_sqe(); fill it; sqe->user_data = loop.uring_user_data(slot, tag);
     // Submissions are flushed once per loop iteration, together with the wait for completions.
-    bool enable_uring(bool quiet = false, unsigned entries = 1024, unsigned buffers = 512, unsigned buffer_size = 4096);
+    // prepare_uring() returns null (reason in *error) when the kernel refuses: io_uring compiled
+    // out or switched off (kernel.io_uring_disabled), blocked by a seccomp profile as in many
+    // container runtimes, or older than Linux 6.1.
+    static std::shared_ptr<Uring> prepare_uring(std::string* error, unsigned entries = 1024, unsigned buffers = 512, unsigned buffer_size = 4096);
+    bool adopt_uring(std::shared_ptr<Uring> prepared);
     bool uring_enabled() const { return uring_ != nullptr; }
     int register_uring_handler(UringHandler* h);
     static uint64_t uring_user_data(int slot, uint32_t tag) { return (static_cast<uint64_t>(slot + 1) << 32) | tag; }
@@ -138,7 +145,7 @@ class EventLoop {
     std::vector<std::function<void()>> mailbox_;
     std::atomic<bool> mailbox_signalled_{false};
     std::vector<std::function<void()>> deferred_;
-    std::unique_ptr<Uring> uring_;
+    std::shared_ptr<Uring> uring_;
     std::vector<UringHandler*> uring_handlers_;
     int64_t spin_ns_ = 0;
     int64_t last_event_ns_ = 0;

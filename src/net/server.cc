@@ -578,7 +578,7 @@ void Worker::on_events(uint32_t /*events*/) {
             return;
         }
         set_nodelay(fd);
-        // The connection is counted at the moment of the decision, not when the target gets round
+            // The connection is counted at the moment of the decision, not when the target gets round
         // to adopting it: several acceptors deciding at the same time must see each other's choices.
         Worker* target = this;
         if (peers_ && peers_->size() > 1 && options_.accept_mode == AcceptMode::kBalanced) {
@@ -762,10 +762,6 @@ void Worker::thread_main() {
     std::snprintf(name, sizeof name, "hola-io-%d", id_);
     pthread_setname_np(pthread_self(), name);
     loop_.refresh_clock();
-    if (options_.io_backend != IoBackend::kEpoll) {
-        uring_active_.store(loop_.enable_uring(/*quiet=*/options_.io_backend == IoBackend::kAuto), std::memory_order_relaxed);
-    }
-    backend_decided_.store(true, std::memory_order_release);
     app_->on_worker_start(*this);
     if (listen_fd_ >= 0) loop_.add(listen_fd_, EPOLLIN, this);
     loop_.set_spin_ns(static_cast<int64_t>(options_.spin_us) * 1000);
@@ -867,12 +863,19 @@ bool Server::start(std::string* error) {
         wp->thread_ = std::thread([wp] { wp->thread_main(); });
     }
     started_ = true;
+    if (options_.io_backend != IoBackend::kEpoll) {
+        ring_thread_ = std::thread([this] { setup_rings(); });
+    } else {
+        rings_done_.store(true, std::memory_order_release);
+    }
     return true;
 }
 
 void Server::stop() {
     if (!started_) return;
     started_ = false;
+    stopping_rings_.store(true, std::memory_order_relaxed);
+    if (ring_thread_.joinable()) ring_thread_.join();
     for (auto& w : workers_) {
         Worker* wp = w.get();
         wp->loop().post([wp] { wp->begin_drain(); });
@@ -900,11 +903,32 @@ ServerStats Server::stats() const {
 
 const char* Server::io_backend_name() const {
     if (options_.io_backend == IoBackend::kEpoll) return "epoll";
-    for (const auto& w : workers_) {
-        while (!w->backend_decided_.load(std::memory_order_acquire)) std::this_thread::yield();  // the first thing a worker does
-        if (!w->uring_active_.load(std::memory_order_relaxed)) return "epoll";
+    size_t active = 0;
+    for (const auto& w : workers_) active += w->uring_active_.load(std::memory_order_relaxed) ? 1 : 0;
+    if (active == workers_.size()) return "uring";
+    if (!rings_done_.load(std::memory_order_acquire)) return "uring (starting)";  // the first few milliseconds
+    return active == 0 ? "epoll" : "mixed";
+}
+
+// Runs on its own short-lived thread: makes one ring per worker, one after the other, and hands
+// each to its worker. The workers serve on epoll meanwhile.
+void Server::setup_rings() {
+    pthread_setname_np(pthread_self(), "hola-rings");
+    for (auto& w : workers_) {
+        if (stopping_rings_.load(std::memory_order_relaxed)) break;
+        std::string why;
+        std::shared_ptr<Uring> ring = EventLoop::prepare_uring(&why);
+        if (!ring) {
+            if (options_.io_backend == IoBackend::kUring)
+                std::fprintf(stderr, "hola: io_uring is not usable here (%s) - staying with epoll\n", why.c_str());
+            break;  // what one ring is refused, the next will be too
+        }
+        Worker* wp = w.get();
+        wp->loop().post([wp, ring] {
+            if (wp->loop().adopt_uring(ring)) wp->uring_active_.store(true, std::memory_order_relaxed);
+        });
     }
-    return "uring";
+    rings_done_.store(true, std::memory_order_release);
 }
 
 std::vector<WorkerSnapshot> Server::worker_stats() const {

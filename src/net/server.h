@@ -23,8 +23,10 @@
 #pragma once
 
 #include <atomic>
+#include <condition_variable>
 #include <cstdint>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <string_view>
 #include <thread>
@@ -153,7 +155,9 @@ enum class AcceptMode : uint8_t {
 //           loop iteration that submits the batch and waits for the next completions. Listeners,
 //           timers, the mailbox and the outbound client stay on epoll, which is polled through the
 //           ring. Falls back to kEpoll when the kernel refuses io_uring. A closed connection keeps
-//           its slot until the completions of its last operations have arrived.
+//           its slot until the completions of its last operations have arrived. A worker starts
+//           on epoll and switches when its ring arrives (a few ms after start-up; connections
+//           accepted before that stay on epoll for their lifetime).
 //   kAuto   kUring where the kernel offers it (Linux >= 6.1, not blocked), else kEpoll, silently.
 //           The default: on the benchmark box kUring serves 5 % more requests per core and cuts
 //           p99 latency by a quarter (profiles/r2_probe4/), and nothing is lost where it is absent.
@@ -261,7 +265,6 @@ class Worker final : public EventHandler {
     void* app_state_ = nullptr;
     std::atomic<double> cpu_seconds_{0};  // filled in when the thread exits
     std::atomic<bool> uring_active_{false};
-    std::atomic<bool> backend_decided_{false};
     std::thread thread_;
 };
 
@@ -279,7 +282,9 @@ class Server {
     int threads() const { return static_cast<int>(workers_.size()); }
     ServerStats stats() const;
     std::vector<WorkerSnapshot> worker_stats() const;
-    // "epoll" or "uring": what the workers actually run on (uring falls back when refused).
+    // "epoll", "uring", "uring (starting)" during the first milliseconds, or "mixed": what the
+    // workers actually run on. Rings are made in the background after start() and handed to the
+    // workers, which serve on epoll until theirs arrives (and for good when the kernel refuses).
     const char* io_backend_name() const;
     Worker& worker(int i) { return *workers_[static_cast<size_t>(i)]; }
 
@@ -290,6 +295,10 @@ class Server {
     std::vector<Worker*> worker_ptrs_;
     uint16_t bound_port_ = 0;
     bool started_ = false;
+    void setup_rings();
+    std::thread ring_thread_;
+    std::atomic<bool> stopping_rings_{false};
+    std::atomic<bool> rings_done_{false};
 };
 
 // Small helper shared with the outbound client.

@@ -33,10 +33,14 @@ class Uring {
     // A kernel that refuses those flags is older than 6.1; with `modern_only` that is an error
     // (-ENOSYS) - such a kernel may lack multishot receives and buffer rings too, which cannot
     // be probed for directly - otherwise a plain ring is tried.
-    int init(unsigned entries, bool modern_only = false) {
+    // `disabled`: the ring is created in the disabled state (IORING_SETUP_R_DISABLED), which lets
+    // one thread create it and register its buffers and another thread - the one that will use
+    // it - take it over with enable().
+    int init(unsigned entries, bool modern_only = false, bool disabled = false) {
         io_uring_params p;
         std::memset(&p, 0, sizeof p);
         p.flags = IORING_SETUP_SINGLE_ISSUER | IORING_SETUP_DEFER_TASKRUN | IORING_SETUP_CQSIZE | IORING_SETUP_CLAMP;
+        if (disabled) p.flags |= IORING_SETUP_R_DISABLED;
         p.cq_entries = entries * 4;
         int fd = static_cast<int>(syscall(__NR_io_uring_setup, entries, &p));
         if (fd < 0 && modern_only) return errno == EINVAL ? -ENOSYS : -errno;
@@ -76,6 +80,10 @@ class Uring {
     }
 
     int fd() const { return fd_; }
+
+    // Takes over a ring created with `disabled`: from now on the calling thread is its only
+    // submitter. Returns 0 or -errno.
+    int enable() { return syscall(__NR_io_uring_register, fd_, IORING_REGISTER_ENABLE_RINGS, nullptr, 0) < 0 ? -errno : 0; }
 
     // Next free submission entry, zeroed; nullptr when the queue is full (submit first).
     io_uring_sqe* get_sqe() {
