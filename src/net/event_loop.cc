@@ -168,8 +168,20 @@ bool EventLoop::adopt_uring(std::shared_ptr<Uring> ring) {
 }
 
 int EventLoop::register_uring_handler(UringHandler* h) {
+    if (!uring_free_slots_.empty()) {
+        const int slot = uring_free_slots_.back();
+        uring_free_slots_.pop_back();
+        uring_handlers_[static_cast<size_t>(slot)] = h;
+        return slot;
+    }
     uring_handlers_.push_back(h);
     return static_cast<int>(uring_handlers_.size()) - 1;
+}
+
+void EventLoop::unregister_uring_handler(int slot) {
+    if (slot < 0 || static_cast<size_t>(slot) >= uring_handlers_.size()) return;
+    uring_handlers_[static_cast<size_t>(slot)] = nullptr;
+    uring_free_slots_.push_back(slot);
 }
 
 io_uring_sqe* EventLoop::uring_sqe() {
@@ -233,7 +245,7 @@ void EventLoop::run_uring() {
                 bid = static_cast<uint16_t>(flags >> IORING_CQE_BUFFER_SHIFT);
                 data = uring_->buffer(bid);
             }
-            if (slot < uring_handlers_.size()) uring_handlers_[slot]->on_completion(static_cast<uint32_t>(user_data), res, flags, data);
+            if (slot < uring_handlers_.size() && uring_handlers_[slot]) uring_handlers_[slot]->on_completion(static_cast<uint32_t>(user_data), res, flags, data);
             if (flags & IORING_CQE_F_BUFFER) uring_->recycle_buffer(bid, true);
         }
         last_event_ns_ = now_ns_;

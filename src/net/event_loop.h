@@ -107,6 +107,8 @@ class EventLoop {
     bool adopt_uring(std::shared_ptr<Uring> prepared);
     bool uring_enabled() const { return uring_ != nullptr; }
     int register_uring_handler(UringHandler* h);
+    // Only once no operation submitted under the slot is in flight any more (the slot is reused).
+    void unregister_uring_handler(int slot);
     static uint64_t uring_user_data(int slot, uint32_t tag) { return (static_cast<uint64_t>(slot + 1) << 32) | tag; }
     ::io_uring_sqe* uring_sqe();  // never null: flushes the submission queue when it is full
     uint16_t uring_buffer_group() const;
@@ -147,6 +149,7 @@ class EventLoop {
     std::vector<std::function<void()>> deferred_;
     std::shared_ptr<Uring> uring_;
     std::vector<UringHandler*> uring_handlers_;
+    std::vector<int> uring_free_slots_;
     int64_t spin_ns_ = 0;
     int64_t last_event_ns_ = 0;
     LoopStats stats_;

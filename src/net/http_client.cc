@@ -1,5 +1,6 @@
 #include "net/http_client.h"
 
+#include <linux/io_uring.h>
 #include <netinet/in.h>
 #include <sys/socket.h>
 #include <unistd.h>
@@ -35,7 +36,13 @@ struct HttpClient::Pending {
     bool cancelled = false;
 };
 
-class HttpClient::Conn final : public EventHandler {
+// A connection starts on epoll (connect() completion is a readiness event). Once established,
+// and if the loop runs an io_uring, it moves there: a multishot receive stays armed for the life
+// of the connection and each request is one queued send - no system call of its own for either,
+// where the epoll path costs a send(), the poll round trip and a recv() per downstream call.
+// A retired connection with operations in flight lingers (closed for business, descriptor shut
+// down) until their completions have arrived, then deletes itself.
+class HttpClient::Conn final : public EventHandler, public UringHandler {
  public:
     enum class State : uint8_t { kConnecting, kSending, kReading, kIdle, kClosed };
 
@@ -78,6 +85,7 @@ class HttpClient::Conn final : public EventHandler {
                 return;
             }
             state_ = State::kSending;
+            if (client_->loop_->uring_enabled()) go_uring();
             write_request();
             return;
         }
@@ -94,12 +102,120 @@ class HttpClient::Conn final : public EventHandler {
     // A keep-alive connection spends its life waiting for input; the interest set only changes
     // around connect() and when a write would block, so most requests need no epoll_ctl at all.
     void set_interest(uint32_t events) {
-        if (events == registered_) return;
+        if (uring_ || events == registered_) return;
         registered_ = events;
         client_->loop_->modify(fd_, events, this);
     }
 
+    enum : uint32_t { kOpRecv = 1, kOpSend = 2 };
+
+    void go_uring() {
+        client_->loop_->remove(fd_);
+        registered_ = 0;
+        uring_ = true;
+        slot_ = client_->loop_->register_uring_handler(this);
+        arm_recv();
+    }
+
+    void arm_recv() {
+        EventLoop& loop = *client_->loop_;
+        io_uring_sqe* sqe = loop.uring_sqe();
+        sqe->opcode = IORING_OP_RECV;
+        sqe->fd = fd_;
+        sqe->ioprio = IORING_RECV_MULTISHOT;
+        sqe->flags = IOSQE_BUFFER_SELECT;
+        sqe->buf_group = loop.uring_buffer_group();
+        sqe->user_data = EventLoop::uring_user_data(slot_, kOpRecv);
+        recv_armed_ = true;
+        ++ops_;
+    }
+
+    void submit_send() {
+        io_uring_sqe* sqe = client_->loop_->uring_sqe();
+        sqe->opcode = IORING_OP_SEND;
+        sqe->fd = fd_;
+        sqe->addr = reinterpret_cast<uint64_t>(send_buf_.data() + sent_);
+        sqe->len = static_cast<uint32_t>(send_buf_.size() - sent_);
+        sqe->msg_flags = MSG_NOSIGNAL;
+        sqe->user_data = EventLoop::uring_user_data(slot_, kOpSend);
+        ++ops_;
+    }
+
+    // Last completion of a retired connection: now the descriptor and the object can go.
+    void reap() {
+        if (state_ != State::kClosed || ops_ > 0 || fd_ < 0) return;
+        close(fd_);
+        fd_ = -1;
+        client_->loop_->unregister_uring_handler(slot_);
+        HttpClient* client = client_;
+        client->zombies_.erase(this);
+        client->loop_->defer([this] { delete this; });
+    }
+
+    void on_completion(uint32_t tag, int32_t res, uint32_t cqe_flags, const char* data) override {
+        if ((tag & 3u) == kOpRecv) {
+            const bool more = (cqe_flags & IORING_CQE_F_MORE) != 0;
+            if (!more) {
+                recv_armed_ = false;
+                --ops_;
+            }
+            if (state_ == State::kClosed) {
+                reap();
+                return;
+            }
+            if (res > 0 && data) {
+                if (state_ == State::kIdle) {
+                    client_->drop_idle(this);  // anything arriving on an idle connection means the peer is done with it
+                    return;
+                }
+                got_bytes_ = true;
+                if (state_ == State::kSending) state_ = State::kReading;  // the answer overtook the send's completion
+                if (!consume(data, static_cast<size_t>(res))) return;
+            } else if (res == 0) {
+                if (state_ == State::kIdle) {
+                    client_->drop_idle(this);
+                } else if (head_done_ && until_close_) {
+                    deliver(false);
+                } else {
+                    client_->retry_or_fail(this, ClientResult::Code::kIoError);
+                }
+                return;
+            } else if (res != -ENOBUFS && res != -EINTR && res != -EAGAIN) {
+                if (state_ == State::kIdle) {
+                    client_->drop_idle(this);
+                } else {
+                    client_->retry_or_fail(this, ClientResult::Code::kIoError);
+                }
+                return;
+            }
+            if (!more && state_ != State::kClosed) arm_recv();
+            return;
+        }
+        // kOpSend
+        --ops_;
+        if (state_ == State::kClosed) {
+            reap();
+            return;
+        }
+        if (res < 0 && res != -EINTR && res != -EAGAIN) {
+            client_->retry_or_fail(this, ClientResult::Code::kIoError);
+            return;
+        }
+        if (res > 0) sent_ += static_cast<size_t>(res);
+        if (sent_ < send_buf_.size()) {
+            submit_send();
+        } else if (state_ == State::kSending) {
+            state_ = State::kReading;
+        }
+    }
+
     void write_request() {
+        if (uring_) {
+            send_buf_.assign(req_->request);  // a copy: the request object may be cancelled while the send is in flight
+            sent_ = 0;
+            submit_send();
+            return;
+        }
         const std::string& r = req_->request;
         while (sent_ < r.size()) {
             const ssize_t n = ::send(fd_, r.data() + sent_, r.size() - sent_, MSG_NOSIGNAL);
@@ -243,6 +359,12 @@ class HttpClient::Conn final : public EventHandler {
     bool reused_ = false;
     bool got_bytes_ = false;
     size_t sent_ = 0;
+    // io_uring mode.
+    bool uring_ = false;
+    int slot_ = -1;
+    int ops_ = 0;
+    bool recv_armed_ = false;
+    std::string send_buf_;
     std::string in_;
     bool head_done_ = false;
     int status_ = 0;
@@ -266,9 +388,15 @@ HttpClient::~HttpClient() {
     *alive_ = false;
     for (Conn* c : conns_) {
         if (c->fd_ >= 0) {
-            loop_->remove(c->fd_);
+            if (!c->uring_) loop_->remove(c->fd_);
+            if (c->uring_) loop_->unregister_uring_handler(c->slot_);  // late completions find an empty slot
             close(c->fd_);
         }
+        delete c;
+    }
+    for (Conn* c : zombies_) {
+        loop_->unregister_uring_handler(c->slot_);
+        if (c->fd_ >= 0) close(c->fd_);
         delete c;
     }
 }
@@ -401,12 +529,23 @@ void HttpClient::drop_idle(Conn* conn) {
 void HttpClient::retire(Conn* conn) {
     if (conn->state_ == Conn::State::kClosed) return;
     conn->state_ = Conn::State::kClosed;
+    conns_.erase(conn);
+    if (conn->uring_ && conn->ops_ > 0) {
+        // Completions are still to come and they carry this object's address: shut the socket
+        // down so that they come now; the last one closes the descriptor and deletes the object.
+        shutdown(conn->fd_, SHUT_RDWR);
+        zombies_.insert(conn);
+        return;
+    }
     if (conn->fd_ >= 0) {
-        loop_->remove(conn->fd_);
+        if (conn->uring_) {
+            loop_->unregister_uring_handler(conn->slot_);
+        } else {
+            loop_->remove(conn->fd_);
+        }
         close(conn->fd_);
         conn->fd_ = -1;
     }
-    conns_.erase(conn);
     // The current batch of epoll events may still point at this object.
     loop_->defer([conn] { delete conn; });
 }

@@ -80,6 +80,7 @@ class HttpClient {
     std::unordered_map<RequestId, std::shared_ptr<Pending>> pending_;
     std::unordered_map<std::string, std::vector<Conn*>> idle_;
     std::unordered_set<Conn*> conns_;
+    std::unordered_set<Conn*> zombies_;  // retired, waiting for the completions of their last io_uring operations
     std::shared_ptr<bool> alive_;  // guards resolver callbacks that outlive the client
 };
 
