@@ -186,13 +186,16 @@ void EventLoop::unregister_uring_handler(int slot) {
 
 io_uring_sqe* EventLoop::uring_sqe() {
     io_uring_sqe* sqe = uring_->get_sqe();
-    if (!sqe) {
-        uring_->submit_and_wait_for(0);  // queue full: hand what is there to the kernel
+    // Queue full: hand what is there to the kernel. That can be refused for a moment (-EBUSY while
+    // completions that overflowed the completion queue wait to be moved into it; run_uring() frees
+    // a slot per completion before dispatching it, so the next attempt makes room).
+    for (int attempt = 0; !sqe && attempt < 1000; ++attempt) {
+        uring_->submit_and_wait_for(0);
         sqe = uring_->get_sqe();
-        if (!sqe) {
-            std::fprintf(stderr, "hola: io_uring submission queue stays full\n");
-            std::abort();
-        }
+    }
+    if (!sqe) {
+        std::fprintf(stderr, "hola: io_uring submission queue stays full\n");
+        std::abort();
     }
     return sqe;
 }
