@@ -11,6 +11,7 @@ is the tooling around it:
 * :func:`hola_b200.loadgen.run`          drive ``build/hola-load`` and parse its JSON report
 * :mod:`hola_b200.client`                a tiny raw-socket HTTP client for byte-exact assertions
 * :mod:`hola_b200.fakes`                 fake aloha / Zipkin / DNS servers for tests and manual trials
+* :mod:`hola_b200.reference`             launcher for the Java reference (or any stand-in) used by ``bench.py --impl reference``
 
 There are deliberately no ``models/``, ``ops/`` or ``parallel/`` sub-packages: the reference has
 no model, tensor op, kernel or collective, and none was invented.
