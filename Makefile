@@ -93,14 +93,15 @@ test: $(BUILD)/hola_tests
 
 # Everything: C++ unit tests, the Python suite, then the black-box part again under both sanitizers.
 BLACKBOX := tests/test_contract.py tests/test_server_core.py tests/test_chaining.py tests/test_tracing.py \
-            tests/test_stream.py tests/test_dns.py tests/test_fuzz.py
+            tests/test_stream.py tests/test_dns.py tests/test_fuzz.py tests/test_cli.py
 check: all
 	$(BUILD)/hola_tests
 	python -m pytest tests -q
+	python -m pytest $(BLACKBOX) -q --io-backend epoll
 	python -m pytest $(BLACKBOX) -q --variant asan
 	python -m pytest $(BLACKBOX) -q --variant tsan
 
 clean:
 	rm -rf build
 
--include $(LIB_OBJ:.o=.d) $(TEST_OBJ:.o=.d) $(BUILD)/obj/app/main.d $(BUILD)/obj/tools/hola_load.d $(BUILD)/obj/tools/hola_coldstart.d $(BUILD)/obj/tools/capi.d
+-include $(LIB_OBJ:.o=.d) $(TEST_OBJ:.o=.d) $(BUILD)/obj/app/main.d $(BUILD)/obj/tools/hola_load.d $(BUILD)/obj/tools/hola_coldstart.d $(BUILD)/obj/tools/capi.d $(BUILD)/obj/tools/null_server.d
