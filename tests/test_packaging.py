@@ -50,6 +50,7 @@ def test_kubernetes_manifest_mirrors_the_fabric8_properties():
     probe = container["readinessProbe"]
     assert probe["httpGet"] == {"path": "/api/health", "port": 8080}  # pom.xml:91-92
     assert probe["initialDelaySeconds"] == 5 and probe["timeoutSeconds"] == 30  # pom.xml:93-94
+    assert "resources" not in container  # the reference sets no limits (pom.xml:69-94); neither does this manifest
     for selector_key, value in svc["spec"]["selector"].items():
         assert labels[selector_key] == value  # the service actually selects the pods
 
