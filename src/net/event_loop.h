@@ -102,7 +102,7 @@ class EventLoop {
     // prepare_uring() returns null (reason in *error) when the kernel refuses: io_uring compiled
     // out or switched off (kernel.io_uring_disabled), blocked by a seccomp profile as in many
     // container runtimes, or older than Linux 6.1.
-    static std::shared_ptr<Uring> prepare_uring(std::string* error, unsigned entries = 1024, unsigned buffers = 512, unsigned buffer_size = 4096);
+    static std::shared_ptr<Uring> prepare_uring(std::string* error, unsigned entries = 1024, unsigned buffers = 512, unsigned buffer_size = 2048);
     bool adopt_uring(std::shared_ptr<Uring> prepared);
     bool uring_enabled() const { return uring_ != nullptr; }
     int register_uring_handler(UringHandler* h);
