@@ -221,8 +221,27 @@ void EventLoop::run_uring() {
     bool epoll_backlog = true;  // whatever the epoll loop left pending when it handed over
     while (!stop_.load(std::memory_order_acquire)) {
         const int timeout_ms = epoll_backlog ? 0 : next_timeout_ms();
-        if (timeout_ms != 0) ++stats_.blocking_waits;
-        const int rc = uring_->submit_and_wait_for(static_cast<int64_t>(timeout_ms) * 1000000);
+        int rc;
+        if (spin_ns_ > 0 && timeout_ms != 0) {
+            // Busy-poll window (set_spin_ns): keep entering without sleeping while traffic is
+            // recent; completions are only posted on entry (DEFER_TASKRUN), so every look is a
+            // system call - the same price the epoll loop pays for its epoll_wait(0).
+            rc = uring_->submit_and_wait_for(0);
+            while (rc == 0 && !uring_->peek()) {
+                const int64_t t = monotonic_ns();
+                if (t - last_event_ns_ >= spin_ns_ || stop_.load(std::memory_order_relaxed)) break;
+                if (!timers_.empty() && timers_.top().deadline <= t) break;
+                __builtin_ia32_pause();
+                rc = uring_->submit_and_wait_for(0);
+            }
+            if (rc == 0 && !uring_->peek() && (timers_.empty() || timers_.top().deadline > monotonic_ns())) {
+                ++stats_.blocking_waits;
+                rc = uring_->submit_and_wait_for(static_cast<int64_t>(timeout_ms) * 1000000);
+            }
+        } else {
+            if (timeout_ms != 0) ++stats_.blocking_waits;
+            rc = uring_->submit_and_wait_for(static_cast<int64_t>(timeout_ms) * 1000000);
+        }
         refresh_clock();
         ++stats_.iterations;
         if (rc != 0 && rc != -ETIME && rc != -EINTR && rc != -EAGAIN && rc != -EBUSY) {
@@ -236,6 +255,7 @@ void EventLoop::run_uring() {
             const uint32_t flags = cqe->flags;
             uring_->seen();
             ++stats_.events;
+            last_event_ns_ = now_ns_;
             if (user_data == kEpollPollTag) {
                 epoll_ready = true;
                 if (!(flags & IORING_CQE_F_MORE)) arm_epoll_poll();
@@ -251,7 +271,6 @@ void EventLoop::run_uring() {
             if (slot < uring_handlers_.size() && uring_handlers_[slot]) uring_handlers_[slot]->on_completion(static_cast<uint32_t>(user_data), res, flags, data);
             if (flags & IORING_CQE_F_BUFFER) uring_->recycle_buffer(bid, true);
         }
-        last_event_ns_ = now_ns_;
         if (epoll_ready || epoll_backlog) {
             // The poll on the epoll descriptor reports *new* readiness only. The epoll set itself
             // is level-triggered and its handlers rely on that (a short read leaves a pending FIN
